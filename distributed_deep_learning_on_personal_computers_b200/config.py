@@ -1,0 +1,161 @@
+"""Run configuration: one dataclass, a CLI, and ``torchrun``-style environment variables.
+
+The reference keeps every knob as a module-level constant that the user edits in the source
+(``R:23-25`` codec flags, ``R:223`` worker count, ``R:685-687`` sync period / batch / width
+divisor, ``R:720`` epochs, ``R:176-177`` address and port, ``R:715``/``R:732`` paths).  Each of
+those constants is a field here and keeps the reference value as its default, so
+``TrainConfig()`` describes the shipped reference run.  ``R`` is
+``/root/reference/Vaihingen PyTorch 2 (кластер).py``.
+"""
+from __future__ import annotations
+
+import argparse
+import dataclasses
+import json
+import os
+from dataclasses import dataclass, field
+from typing import Optional
+
+CODECS = ("fp32", "bf16", "fp16", "q201", "q21", "int8s", "fp8")
+# Names the reference uses for its ``model_bytes`` switch (R:25) -> our codec names.
+REFERENCE_CODEC_ALIASES = {"float32": "fp32", "float16": "q201", "int8": "q21"}
+
+
+@dataclass
+class TrainConfig:
+    # ---- model (R:620-656, R:687, R:702) -------------------------------------------------
+    base_channels: int = 32          # 64 // NN_in_model with NN_in_model = 2 (R:687)
+    out_classes: int = 6             # R:702
+    in_channels: int = 3
+    up_sample_mode: str = "conv_transpose"   # or "bilinear" (R:605-612)
+    # ---- data (R:661-674, R:737-741) ------------------------------------------------------
+    data_dir: Optional[str] = None   # None -> synthetic Vaihingen-shaped tiles
+    tile: int = 512                  # R:737
+    train_tiles: int = 127           # R:737 (157 files - 30 held out)
+    holdout_tiles: int = 30          # R:672-673
+    shard_data: bool = True          # the reference does not shard; we do by default
+    shuffle: bool = True
+    # ---- optimisation (R:685-686, R:703-704, R:720) --------------------------------------
+    batch_size: int = 1              # per-rank micro-batch (R:686)
+    sync_every: int = 50             # frequency_sending_gradients (R:685)
+    epochs: int = 100                # R:720
+    optimizer: str = "adam"          # R:704; "sgd" also available
+    lr: float = 1e-3
+    betas: tuple = (0.9, 0.999)
+    eps: float = 1e-8
+    weight_decay: float = 0.0
+    momentum: float = 0.0            # sgd only
+    accumulate: str = "mean"         # "mean" over the K micro-batches, or "sum" (reference, Q8)
+    reduce: str = "mean"             # "mean" over ranks, or "sum" (reference with one worker, Q1)
+    flush_at_epoch_end: bool = True  # the reference leaks the tail of an epoch into the next (Q7)
+    max_steps: Optional[int] = None  # stop after this many micro-batches (for tests / smoke)
+    # ---- gradient exchange (R:23-25, R:43-69, R:255-556) ---------------------------------
+    codec: str = "q201"              # model_bytes = 'float16' in the reference (R:25)
+    requantize_output: bool = False  # the reference quantizes the reduced gradient again (Q6)
+    compress: bool = True            # compress_model (R:24); only the TCP-star transport deflates
+    compress_level: int = 1          # mgzip compresslevel (R:51)
+    compress_threads: int = 12       # mgzip thread count (R:43)
+    compress_block: int = 1_000_000  # mgzip blocksize (R:51)
+    comm: str = "auto"               # auto | native | torch | star
+    bucket_mb: float = 25.0
+    # ---- runtime ---------------------------------------------------------------------------
+    device: str = "auto"             # auto | cuda | cpu
+    dtype: str = "auto"              # auto | bf16 | fp32
+    backend: str = "auto"            # auto | nccl | gloo
+    engine: str = "auto"             # auto | native (sm_100a kernels) | torch (autograd oracle path)
+    cuda_graph: bool = True
+    seed: int = 0
+    # ---- rendezvous (R:173-206, R:223-251) -------------------------------------------------
+    master_addr: str = "127.0.0.1"   # the reference hard-codes an address (Q17); never copied
+    master_port: int = 5005          # R:177
+    world_size: int = 2              # N_conn + 1 with N_conn = 1 (R:223)
+    rank: int = 0
+    local_rank: int = 0
+    timeout_s: float = 600.0         # the reference blocks forever
+    # ---- outputs (R:715-716, R:781-790) ----------------------------------------------------
+    out_dir: str = "runs/default"
+    log_name: Optional[str] = None   # default otus_{codec}.txt, as in R:715
+    sample_images: int = 5           # R:785
+    save_every_epochs: int = 1
+    resume: Optional[str] = None
+    eval_holdout: bool = True        # the reference never evaluates its hold-out
+
+    # ------------------------------------------------------------------------------------
+    def __post_init__(self):
+        self.codec = REFERENCE_CODEC_ALIASES.get(self.codec, self.codec)
+        if self.codec not in CODECS:
+            raise ValueError(f"unknown codec {self.codec!r}; choose from {CODECS}")
+        if self.up_sample_mode not in ("conv_transpose", "bilinear"):
+            raise ValueError("Unsupported `up_sample_mode` (conv_transpose | bilinear)")
+        if self.accumulate not in ("mean", "sum") or self.reduce not in ("mean", "sum"):
+            raise ValueError("accumulate / reduce must be 'mean' or 'sum'")
+        if self.tile % 32:
+            raise ValueError("tile must be a multiple of 32 (five 2x2 pools, R:644-648)")
+        self.betas = tuple(self.betas)
+
+    @property
+    def global_batch(self) -> int:
+        """Per-sync global batch, as printed in the reference's log header (R:716)."""
+        return self.batch_size * self.world_size
+
+    def log_file(self) -> str:
+        return os.path.join(self.out_dir, self.log_name or f"otus_{self.codec}.txt")
+
+    def to_dict(self) -> dict:
+        return dataclasses.asdict(self)
+
+    @classmethod
+    def from_dict(cls, d: dict) -> "TrainConfig":
+        names = {f.name for f in dataclasses.fields(cls)}
+        return cls(**{k: v for k, v in d.items() if k in names})
+
+    def apply_env(self) -> "TrainConfig":
+        """Fill rank / world / rendezvous from the variables ``torchrun`` exports."""
+        env = os.environ
+        if "RANK" in env:
+            self.rank = int(env["RANK"])
+        if "WORLD_SIZE" in env:
+            self.world_size = int(env["WORLD_SIZE"])
+        if "LOCAL_RANK" in env:
+            self.local_rank = int(env["LOCAL_RANK"])
+        if "MASTER_ADDR" in env:
+            self.master_addr = env["MASTER_ADDR"]
+        if "MASTER_PORT" in env:
+            self.master_port = int(env["MASTER_PORT"])
+        return self
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(
+        prog="python -m distributed_deep_learning_on_personal_computers_b200",
+        description="B200-native data-parallel U-Net segmentation trainer")
+    for f in dataclasses.fields(TrainConfig):
+        name = "--" + f.name.replace("_", "-")
+        default = f.default if f.default is not dataclasses.MISSING else None
+        if f.type in ("bool", bool):
+            p.add_argument(name, type=lambda s: s.lower() in ("1", "true", "yes", "on"),
+                           default=default, metavar="BOOL")
+        elif f.name == "betas":
+            p.add_argument(name, type=float, nargs=2, default=default)
+        elif f.type in ("int", int):
+            p.add_argument(name, type=int, default=default)
+        elif f.type in ("float", float):
+            p.add_argument(name, type=float, default=default)
+        elif f.type in ("Optional[int]",):
+            p.add_argument(name, type=int, default=default)
+        else:
+            p.add_argument(name, type=str, default=default)
+    p.add_argument("--config", type=str, default=None, help="JSON file with TrainConfig fields")
+    return p
+
+
+def parse_cli(argv=None) -> TrainConfig:
+    args = vars(build_parser().parse_args(argv))
+    path = args.pop("config")
+    if path:
+        with open(path) as fh:
+            base = json.load(fh)
+        base.update({k: v for k, v in args.items()
+                     if v != getattr(TrainConfig, k, None) and v is not None})
+        args = base
+    return TrainConfig.from_dict(args).apply_env()

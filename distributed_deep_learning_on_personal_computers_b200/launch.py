@@ -1,0 +1,26 @@
+"""Entry point: parse the config, join the job, train (the reference's L6, ``R:690`` / ``R:792``)."""
+from __future__ import annotations
+
+import json
+import sys
+
+from .config import parse_cli
+from .trainer import Trainer
+
+
+def main(argv=None) -> int:
+    cfg = parse_cli(argv)
+    if cfg.world_size == 1 and cfg.rank == 0:
+        pass
+    trainer = Trainer(cfg)
+    try:
+        last = trainer.fit()
+        if trainer.ctx.is_coordinator:
+            print(json.dumps({k: v for k, v in last.items()}, default=float))
+    finally:
+        trainer.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,289 @@
+"""Static-shape training engine for the U-Net: explicit forward, loss and backward.
+
+The reference's training step is ``model(x) -> CrossEntropyLoss -> loss.backward()`` through
+eager autograd (``R:754-756``), one library kernel per module.  Here the step is a fixed plan
+over pre-allocated NHWC buffers:
+
+* no autograd tape and no allocator traffic in the hot loop, so the whole micro-batch (and the
+  optimizer step) is capturable in one CUDA graph;
+* ``torch.cat`` (``R:616``) does not exist: the encoder's BN+ReLU kernel and the transposed-conv
+  epilogue write into channel slices of one concat buffer per decoder level;
+* BN statistics come out of the conv epilogue, BN-apply+ReLU(+2x2 max-pool) is one pass, the
+  1x1 head + softmax cross-entropy + accuracy + the head's whole backward is one pass;
+* weight gradients are accumulated in fp32 straight into the flat gradient buffer that the
+  all-reduce and the fused optimizer work on (``models.unet.UNet.flatten_parameters``).
+
+Every op goes through ``ops.functional`` which runs the sm_100a kernel on a B200 and the
+plain-PyTorch oracle (``ops.reference``) on CPU, so this file is testable against autograd of
+``models.unet.UNet.forward`` on any machine.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from ..ops import functional as Fn
+from .unet import UNet, ConvSpec
+
+IN_PAD = 16   # the 3 input channels are zero-padded to one UMMA K-step (16 bf16)
+
+
+@dataclass
+class _Stage:
+    """One conv3x3+BN+ReLU stage and the tensors it owns."""
+    spec: ConvSpec
+    x: torch.Tensor = None            # input activation (N,H,W,Cin) (maybe a concat buffer)
+    y: torch.Tensor = None            # raw conv output (N,H,W,Cout)
+    out: torch.Tensor = None          # activated output (maybe a slice of a concat buffer)
+    pool: Optional[torch.Tensor] = None
+    ss: torch.Tensor = None           # (4,C) scale, shift, mean, invstd of this micro-batch
+    stats: torch.Tensor = None
+    dy: torch.Tensor = None           # gradient w.r.t. y
+    d_out: Optional[torch.Tensor] = None   # gradient w.r.t. out   (set by the consumer)
+    d_pool: Optional[torch.Tensor] = None  # gradient w.r.t. pool  (set by the consumer)
+    dx: Optional[torch.Tensor] = None      # where to write the data gradient (None = skip)
+
+
+class NativeEngine:
+    """Runs forward + loss + backward of one micro-batch over the model's flat buffers."""
+
+    def __init__(self, model: UNet, batch: int, height: int, width: int,
+                 act_dtype: Optional[torch.dtype] = None, conv_impl: str = "auto"):
+        if height % 32 or width % 32:
+            raise ValueError("H and W must be multiples of 32 (five 2x2 pools, R:644-648)")
+        self.model = model
+        flat = model.flat
+        self.flat_p, self.flat_g, self.offsets = flat["param"], flat["grad"], flat["offsets"]
+        self.device = self.flat_p.device
+        self.on_gpu = self.device.type == "cuda"
+        self.act_dtype = act_dtype or (torch.bfloat16 if self.on_gpu else torch.float32)
+        self.conv_impl = conv_impl
+        self.N, self.H, self.W = batch, height, width
+        self.classes = model.out_classes
+        self.bilinear = model.up_sample_mode == "bilinear"
+        # low-precision copy of the weights that the tensor-core kernels read
+        if self.act_dtype == torch.float32:
+            self.flat_lp = self.flat_p
+        else:
+            self.flat_lp = self.flat_p.to(self.act_dtype)
+        self._params = dict(model.named_parameters())
+        self._buffers = dict(model.named_buffers())
+        self._build()
+        self.training = True
+
+    # -- helpers -------------------------------------------------------------------------------
+    def _new(self, *shape, dtype=None):
+        return torch.zeros(*shape, dtype=dtype or self.act_dtype, device=self.device)
+
+    def _seg(self, flat: torch.Tensor, name: str) -> torch.Tensor:
+        off, n = self.offsets[name]
+        return flat[off:off + n]
+
+    def _w3(self, flat: torch.Tensor, name: str) -> torch.Tensor:
+        p = self._params[name]
+        co, ci = p.shape[0], p.shape[1]
+        return self._seg(flat, name).view(co, 3, 3, ci)
+
+    @torch.no_grad()
+    def refresh_lowp(self) -> None:
+        """Re-cast the weights after an optimizer step that did not do it itself."""
+        if self.flat_lp is not self.flat_p:
+            self.flat_lp.copy_(self.flat_p)
+
+    # -- plan ------------------------------------------------------------------------------------
+    def _build(self) -> None:
+        m, N, H, W = self.model, self.N, self.H, self.W
+        specs = m.conv_specs()
+        b = m.base_channels
+        wd = [b, 2 * b, 4 * b, 8 * b, 8 * b]
+        c_up = {5: wd[4], 4: wd[3], 3: wd[3], 2: wd[2], 1: wd[1]}
+        c_skip = {i: wd[i - 1] for i in range(1, 6)}
+        self.c_up, self.c_skip = c_up, c_skip
+        res = lambda lvl: (H >> lvl, W >> lvl)
+
+        self.x_in = self._new(N, H, W, IN_PAD)
+        # concat buffers, one per decoder level i: [up (c_up) | skip (c_skip)]  (R:616 order)
+        self.cat = {i: self._new(N, *res(i - 1), c_up[i] + c_skip[i]) for i in range(1, 6)}
+        self.d_cat = {i: self._new(N, *res(i - 1), c_up[i] + c_skip[i]) for i in range(1, 6)}
+
+        self.stages: Dict[str, Tuple[_Stage, _Stage]] = {}
+        order: List[_Stage] = []
+        x = self.x_in
+        d_x = None
+        for i in range(1, 6):                                   # encoder
+            s0, s1 = (_Stage(sp) for sp in specs[f"down_conv{i}"])
+            h, w = res(i - 1)
+            c = wd[i - 1]
+            s0.x, s0.y, s0.out = x, self._new(N, h, w, c), self._new(N, h, w, c)
+            s0.dy, s0.dx = self._new(N, h, w, c), d_x
+            s1.x, s1.y = s0.out, self._new(N, h, w, c)
+            s1.out = self.cat[i][..., c_up[i]:]
+            s1.pool = self._new(N, h // 2, w // 2, c)
+            s1.dy = self._new(N, h, w, c)
+            s1.dx = s0.d_out = self._new(N, h, w, c)
+            s1.d_out = self.d_cat[i][..., c_up[i]:]
+            s1.d_pool = self._new(N, h // 2, w // 2, c)
+            x, d_x = s1.pool, s1.d_pool
+            self.stages[f"down_conv{i}"] = (s0, s1)
+            order += [s0, s1]
+        s0, s1 = (_Stage(sp) for sp in specs["double_conv"])      # bottleneck
+        h, w = res(5)
+        c = wd[4]
+        s0.x, s0.y, s0.out, s0.dy, s0.dx = x, self._new(N, h, w, c), self._new(N, h, w, c), \
+            self._new(N, h, w, c), d_x
+        s1.x, s1.y, s1.out, s1.dy = s0.out, self._new(N, h, w, c), self._new(N, h, w, c), \
+            self._new(N, h, w, c)
+        s1.dx = s0.d_out = self._new(N, h, w, c)
+        s1.d_out = self._new(N, h, w, c)
+        self.stages["double_conv"] = (s0, s1)
+        order += [s0, s1]
+        below, d_below = s1.out, s1.d_out
+        self.up_io = {}
+        for i in (5, 4, 3, 2, 1):                                # decoder
+            s0, s1 = (_Stage(sp) for sp in specs[f"up_conv{i}"])
+            h, w = res(i - 1)
+            c = s0.spec.cout
+            self.up_io[i] = (below, d_below)
+            s0.x, s0.y, s0.out, s0.dy = self.cat[i], self._new(N, h, w, c), \
+                self._new(N, h, w, c), self._new(N, h, w, c)
+            s0.dx = self.d_cat[i]
+            s1.x, s1.y, s1.out, s1.dy = s0.out, self._new(N, h, w, c), self._new(N, h, w, c), \
+                self._new(N, h, w, c)
+            s1.dx = s0.d_out = self._new(N, h, w, c)
+            s1.d_out = self._new(N, h, w, c)
+            below, d_below = s1.out, s1.d_out
+            self.stages[f"up_conv{i}"] = (s0, s1)
+            order += [s0, s1]
+        self.order = order
+        self.head_in, self.d_head_in = below, d_below
+        for st in order:
+            st.ss = self._new(4, st.spec.cout, dtype=torch.float32)
+        self.loss_acc = self._new(2, dtype=torch.float32)       # [loss sum, correct] of last call
+        self.pred = torch.zeros(N, H, W, dtype=torch.uint8, device=self.device)
+        self.labels = torch.zeros(N, H, W, dtype=torch.uint8, device=self.device)
+
+    # -- one stage ---------------------------------------------------------------------------------
+    def _stage_fwd(self, st: _Stage) -> None:
+        sp = st.spec
+        w = self._w3(self.flat_lp, sp.name + ".weight")
+        bias = self._seg(self.flat_p, sp.name + ".bias")
+        st.stats = Fn.conv3x3_fwd(st.x, w, bias, st.y, want_stats=self.training,
+                                  impl=self.conv_impl)
+        bn = sp.bn
+        Fn.bn_finalize(st.stats, st.y.shape[0] * st.y.shape[1] * st.y.shape[2],
+                       self._seg(self.flat_p, bn + ".weight"), self._seg(self.flat_p, bn + ".bias"),
+                       self._buffers[bn + ".running_mean"], self._buffers[bn + ".running_var"],
+                       self._buffers[bn + ".num_batches_tracked"], st.ss, training=self.training)
+        Fn.bn_relu_pool_fwd(st.y, st.ss, st.out, st.pool)
+
+    def _stage_bwd(self, st: _Stage, need_dx: bool = True) -> None:
+        sp = st.spec
+        bn = sp.bn
+        Fn.bn_relu_pool_bwd(st.d_out, st.d_pool if st.pool is not None else None, st.y, st.ss,
+                            self._seg(self.flat_p, bn + ".weight"),
+                            self._seg(self.flat_g, bn + ".weight"),
+                            self._seg(self.flat_g, bn + ".bias"),
+                            self._seg(self.flat_g, sp.name + ".bias"), st.dy)
+        Fn.conv3x3_wgrad(st.x, st.dy, self._w3(self.flat_g, sp.name + ".weight"),
+                         impl=self.conv_impl)
+        if need_dx and st.dx is not None:
+            Fn.conv3x3_dgrad(st.dy, self._w3(self.flat_lp, sp.name + ".weight"), st.dx,
+                             impl=self.conv_impl)
+
+    # -- public steps --------------------------------------------------------------------------------
+    @torch.no_grad()
+    def load_batch(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> None:
+        """Device-side input preparation (R:737-741): u8 HWC -> /255 -> padded NHWC; labels u8."""
+        Fn.prep_input(images_u8, self.x_in)
+        self.labels.copy_(labels_u8, non_blocking=True)
+
+    @torch.no_grad()
+    def forward(self) -> None:
+        for i in range(1, 6):
+            s0, s1 = self.stages[f"down_conv{i}"]
+            self._stage_fwd(s0)
+            self._stage_fwd(s1)
+        s0, s1 = self.stages["double_conv"]
+        self._stage_fwd(s0)
+        self._stage_fwd(s1)
+        for i in (5, 4, 3, 2, 1):
+            below, _ = self.up_io[i]
+            up_slice = self.cat[i][..., :self.c_up[i]]
+            if self.bilinear:
+                Fn.upsample_bilinear2x_fwd(below, up_slice)
+            else:
+                name = f"up_conv{i}.up_sample"
+                Fn.convT2x2_fwd(below, self._params[name + ".weight"],
+                                self._convT_lp(name), self._seg(self.flat_p, name + ".bias"),
+                                up_slice)
+            s0, s1 = self.stages[f"up_conv{i}"]
+            self._stage_fwd(s0)
+            self._stage_fwd(s1)
+
+    def _convT_lp(self, name: str) -> torch.Tensor:
+        p = self._params[name + ".weight"]
+        ci, co = p.shape[0], p.shape[1]
+        return self._seg(self.flat_lp, name + ".weight").view(4 * co, ci)
+
+    def _head(self, with_grad: bool, grad_scale: float) -> None:
+        wh = self._seg(self.flat_p, "conv_last.weight").view(self.classes, -1)
+        bh = self._seg(self.flat_p, "conv_last.bias")
+        if with_grad:
+            dwh = self._seg(self.flat_g, "conv_last.weight").view(self.classes, -1)
+            dbh = self._seg(self.flat_g, "conv_last.bias")
+            Fn.head_ce_fwd_bwd(self.head_in, wh, bh, self.labels, grad_scale, self.d_head_in,
+                               dwh, dbh, self.pred, self.loss_acc)
+        else:
+            Fn.head_ce_fwd_bwd(self.head_in, wh, bh, self.labels, 0.0, None, None, None,
+                               self.pred, self.loss_acc)
+
+    @torch.no_grad()
+    def backward(self) -> None:
+        for i in (1, 2, 3, 4, 5):
+            s0, s1 = self.stages[f"up_conv{i}"]
+            self._stage_bwd(s1)
+            self._stage_bwd(s0)
+            below, d_below = self.up_io[i]
+            d_up = self.d_cat[i][..., :self.c_up[i]]
+            if self.bilinear:
+                Fn.upsample_bilinear2x_bwd(d_up, d_below)
+            else:
+                name = f"up_conv{i}.up_sample"
+                Fn.convT2x2_bwd(below, d_up, self._params[name + ".weight"], self._convT_lp(name),
+                                self._params[name + ".weight"].grad,
+                                self._seg(self.flat_g, name + ".bias"), d_below)
+        s0, s1 = self.stages["double_conv"]
+        self._stage_bwd(s1)
+        self._stage_bwd(s0)
+        for i in (5, 4, 3, 2, 1):
+            s0, s1 = self.stages[f"down_conv{i}"]
+            self._stage_bwd(s1)
+            self._stage_bwd(s0, need_dx=(i != 1))
+
+    @torch.no_grad()
+    def train_microbatch(self, loss_scale: Optional[float] = None) -> torch.Tensor:
+        """Forward + loss + backward on the batch already in ``x_in`` / ``labels``.
+
+        Gradients are ACCUMULATED into the flat gradient buffer (R:756 semantics).  Returns the
+        device tensor ``[loss_sum, correct]`` (read it back only when logging).
+        """
+        self.training = True
+        pixels = self.N * self.H * self.W
+        self.forward()
+        self._head(True, (1.0 / pixels) if loss_scale is None else loss_scale)
+        self.backward()
+        return self.loss_acc
+
+    @torch.no_grad()
+    def evaluate(self) -> torch.Tensor:
+        """Forward only with running statistics (the reference never does this)."""
+        self.training = False
+        self.forward()
+        self._head(False, 0.0)
+        self.training = True
+        return self.loss_acc
+
+    def logits_free_prediction(self) -> torch.Tensor:
+        return self.pred

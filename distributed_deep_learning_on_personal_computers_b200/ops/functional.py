@@ -1,0 +1,256 @@
+"""Dispatch between the sm_100a kernels (``csrc/``, loaded from the in-tree shared library) and
+the plain-PyTorch oracles (``ops.reference``).
+
+Rule: a CUDA tensor ALWAYS goes to the native kernel.  If the shared library is missing on a
+GPU box the call raises instead of silently running a PyTorch fallback (set
+``B200SEG_ALLOW_FALLBACK=1`` to override, e.g. to produce oracle values on the GPU in a test).
+CPU tensors run the oracle.  The two conv implementations selectable with ``impl`` are
+``"tcgen05"`` (ours) and ``"cudnn"`` (library; used only as a comparison arm and oracle).
+
+``launch_count()`` returns how many of OUR kernels were launched since the last reset; bench.py
+reports it as ``gpu_launches``.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from . import reference as ref
+from . import loader
+
+_LAUNCHES = 0
+
+
+def _tick(n: int = 1) -> None:
+    global _LAUNCHES
+    _LAUNCHES += n
+
+
+def launch_count() -> int:
+    return _LAUNCHES
+
+
+def reset_launch_count() -> None:
+    global _LAUNCHES
+    _LAUNCHES = 0
+
+
+def native_available() -> bool:
+    return loader.library() is not None
+
+
+def _native(t: torch.Tensor) -> bool:
+    """True -> run the sm_100a kernel.  Raises on a GPU tensor without the library."""
+    if not t.is_cuda:
+        return False
+    if loader.library() is not None:
+        return True
+    if os.environ.get("B200SEG_ALLOW_FALLBACK") == "1":
+        return False
+    raise RuntimeError(
+        "CUDA tensor passed to a b200seg op but the native library is not built/loaded "
+        f"({loader.load_error()}). Run `python -c 'import __graft_entry__ as g; g.build()'`.")
+
+
+def _ops():
+    return torch.ops.b200seg
+
+
+def _conv_impl(impl: Optional[str]) -> str:
+    impl = impl or "auto"
+    if impl == "auto":
+        impl = os.environ.get("B200SEG_CONV", "tcgen05")
+    return impl
+
+
+# ---------------------------------------------------------------------------------------------
+def conv3x3_fwd(x, w, bias, y, want_stats=True, impl=None):
+    """y = conv3x3(x, w) + bias; returns the BN statistics handle (see ``bn_finalize``)."""
+    if _native(x):
+        if _conv_impl(impl) == "cudnn":
+            cin = w.shape[3]
+            yy = torch.nn.functional.conv2d(x[..., :cin].permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
+                                            bias.to(x.dtype), padding=1)
+            y.copy_(yy.permute(0, 2, 3, 1))
+            if not want_stats:
+                return None
+            part = torch.empty(_ops().stats_rows(), 2, y.shape[-1], dtype=torch.float32,
+                               device=y.device)
+            _ops().channel_stats(y, part)
+            _tick()
+            return part
+        part = None
+        if want_stats:
+            part = torch.empty(_ops().stats_rows(), 2, y.shape[-1], dtype=torch.float32,
+                               device=y.device)
+        _ops().conv3x3_fwd(x, w, bias, y, part)
+        _tick()
+        return part
+    yy, stats = ref.conv3x3_fwd(x, w, bias, want_stats)
+    y.copy_(yy)
+    return stats
+
+
+def conv3x3_dgrad(dy, w, dx, impl=None):
+    if _native(dy):
+        if _conv_impl(impl) == "cudnn":
+            g = torch.nn.functional.conv_transpose2d(dy.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
+                                                     padding=1)
+            dx.copy_(g.permute(0, 2, 3, 1))
+            return dx
+        _ops().conv3x3_dgrad(dy, w, dx)
+        _tick()
+        return dx
+    return ref.conv3x3_dgrad(dy, w, dx)
+
+
+def conv3x3_wgrad(x, dy, dw, impl=None):
+    if _native(x):
+        if _conv_impl(impl) == "cudnn":
+            cout, _, _, cin = dw.shape
+            g = torch.nn.grad.conv2d_weight(x[..., :cin].permute(0, 3, 1, 2), (cout, cin, 3, 3),
+                                            dy.permute(0, 3, 1, 2), padding=1)
+            dw.add_(g.permute(0, 2, 3, 1))
+            return dw
+        _ops().conv3x3_wgrad(x, dy, dw)
+        _tick()
+        return dw
+    return ref.conv3x3_wgrad(x, dy, dw)
+
+
+def bn_finalize(stats, count, gamma, beta, running_mean, running_var, num_batches_tracked, ss,
+                momentum=0.1, eps=1e-5, training=True):
+    if _native(ss):
+        _ops().bn_finalize(stats, int(count), gamma, beta, running_mean, running_var,
+                           num_batches_tracked, ss, float(momentum), float(eps), bool(training))
+        _tick()
+        return ss
+    out = ref.bn_finalize(stats, count, gamma, beta, running_mean, running_var, momentum, eps,
+                          training)
+    if training:
+        num_batches_tracked.add_(1)
+    ss.copy_(out)
+    return ss
+
+
+def bn_relu_pool_fwd(y, ss, out, pool=None):
+    if _native(y):
+        _ops().bn_relu_pool_fwd(y, ss, out, pool)
+        _tick()
+        return
+    ref.bn_relu_pool_fwd(y, ss, out, pool)
+
+
+def bn_relu_pool_bwd(d_out, d_pool, y, ss, gamma, dgamma, dbeta, dbias, dy):
+    if _native(y):
+        _ops().bn_relu_pool_bwd(d_out, d_pool, y, ss, gamma, dgamma, dbeta, dbias, dy)
+        _tick(2)
+        return
+    ref.bn_relu_pool_bwd(d_out, d_pool, y, ss, gamma, dgamma, dbeta, dbias, dy)
+
+
+def convT2x2_fwd(x, w_param, w_lp, bias, out):
+    """``w_param``: logical (Cin,Cout,2,2) fp32 parameter; ``w_lp``: (4*Cout, Cin) kernel copy."""
+    if _native(x):
+        _ops().convT2x2_fwd(x, w_lp, bias, out)
+        _tick()
+        return
+    ref.convT2x2_fwd(x, w_param, bias, out)
+
+
+def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx):
+    if _native(x):
+        co = w_lp.shape[0] // 4
+        _ops().convT2x2_bwd(x, d_up, w_lp, _flat_of(dw_param).view(4 * co, -1), dbias, dx)
+        _tick(2)
+        return
+    ref.convT2x2_bwd(x, d_up, w_param, dw_param, dbias, dx)
+
+
+def _flat_of(p_view: torch.Tensor) -> torch.Tensor:
+    """Memory-order (dy, dx, Cout, Cin) view of a transposed-conv parameter view."""
+    return p_view.permute(2, 3, 1, 0)
+
+
+def upsample_bilinear2x_fwd(x, out):
+    if _native(x):
+        _ops().upsample_bilinear2x_fwd(x, out)
+        _tick()
+        return
+    ref.upsample_bilinear2x_fwd(x, out)
+
+
+def upsample_bilinear2x_bwd(d_up, dx):
+    if _native(d_up):
+        _ops().upsample_bilinear2x_bwd(d_up, dx)
+        _tick()
+        return
+    ref.upsample_bilinear2x_bwd(d_up, dx)
+
+
+def head_ce_fwd_bwd(a, w, b, labels, grad_scale, da, dw, db, pred, loss_acc):
+    if _native(a):
+        _ops().head_ce_fwd_bwd(a, w, b, labels, float(grad_scale), da, dw, db, pred, loss_acc)
+        _tick()
+        return loss_acc
+    loss_acc.copy_(ref.head_ce_fwd_bwd(a, w, b, labels, grad_scale, da, dw, db, pred))
+    return loss_acc
+
+
+def fused_adam(p, g, m, v, step, lr, beta1, beta2, eps, weight_decay, grad_scale=1.0,
+               p_lowp=None, zero_grad=False):
+    if _native(p):
+        bc1 = 1.0 - beta1 ** step
+        bc2 = 1.0 - beta2 ** step
+        _ops().fused_adam(p, g, m, v, float(lr), float(beta1), float(beta2), float(eps),
+                          float(weight_decay), float(grad_scale), float(bc1), float(bc2),
+                          p_lowp, bool(zero_grad))
+        _tick()
+        return
+    ref.fused_adam(p, g, m, v, step, lr, beta1, beta2, eps, weight_decay, grad_scale,
+                   None if p_lowp is p else p_lowp, zero_grad)
+
+
+def fused_sgd(p, g, buf, lr, momentum, weight_decay, grad_scale=1.0, p_lowp=None,
+              zero_grad=False, first_step=False):
+    if _native(p):
+        _ops().fused_sgd(p, g, buf, float(lr), float(momentum), float(weight_decay),
+                         float(grad_scale), p_lowp, bool(zero_grad), bool(first_step))
+        _tick()
+        return
+    ref.fused_sgd(p, g, buf, lr, momentum, weight_decay, grad_scale,
+                  None if p_lowp is p else p_lowp, zero_grad, first_step)
+
+
+def prep_input(img_u8, out):
+    if _native(out):
+        _ops().prep_input(img_u8, out)
+        _tick()
+        return
+    ref.prep_input(img_u8, out)
+
+
+# -- codecs (parallel.codecs) ------------------------------------------------------------------
+def codec_amax(flat):
+    out = torch.zeros((), dtype=torch.float32, device=flat.device)
+    _ops().amax(flat, out)
+    _tick()
+    return out
+
+
+def codec_encode(flat, scale, codec):
+    payload = torch.empty(flat.numel(), dtype=codec.wire_dtype, device=flat.device)
+    _ops().codec_encode(flat, scale, payload.view(torch.uint8), codec.name)
+    _tick()
+    return payload
+
+
+def codec_decode(payload, scale, codec, out=None, accumulate=False):
+    if out is None:
+        out = torch.empty(payload.numel(), dtype=torch.float32, device=payload.device)
+        accumulate = False
+    _ops().codec_decode(payload.view(torch.uint8), scale, out, codec.name, bool(accumulate))
+    _tick()
+    return out

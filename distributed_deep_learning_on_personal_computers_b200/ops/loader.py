@@ -1,0 +1,88 @@
+"""Finds, builds and loads the in-tree native library ``lib/libb200seg.so``.
+
+The library holds every sm_100a kernel plus their ``extern "C"`` launchers (``include/b200seg.h``)
+and a ``TORCH_LIBRARY`` binding (``csrc/bindings.cpp``), so one file serves ``torch.ops.b200seg.*``
+and plain C callers.  It is built in-tree (``build()``; ninja through ``torch.utils.cpp_extension``)
+with ``-gencode arch=compute_100a,code=sm_100a`` and shipped to GPU boxes as a file; importing the
+package never compiles anything.
+"""
+from __future__ import annotations
+
+import glob
+import os
+import shutil
+from typing import Optional
+
+import torch
+
+PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REPO_DIR = os.path.dirname(PKG_DIR)
+CSRC_DIR = os.path.join(REPO_DIR, "csrc")
+LIB_DIR = os.path.join(PKG_DIR, "lib")
+LIB_PATH = os.path.join(LIB_DIR, "libb200seg.so")
+
+_lib_loaded: Optional[str] = None
+_load_error: Optional[str] = None
+_tried = False
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-lineinfo", "-std=c++17", "--use_fast_math",
+    "--expt-relaxed-constexpr", "-Xptxas", "-v",
+    "-U__CUDA_NO_HALF_OPERATORS__", "-U__CUDA_NO_HALF_CONVERSIONS__",
+    "-U__CUDA_NO_BFLOAT16_CONVERSIONS__", "-U__CUDA_NO_HALF2_OPERATORS__",
+]
+
+
+def sources() -> list:
+    out = []
+    for pat in ("*.cpp", "*.cu", "*/*.cpp", "*/*.cu"):
+        out += glob.glob(os.path.join(CSRC_DIR, pat))
+    return sorted(s for s in out if not os.path.basename(s).startswith("standalone_"))
+
+
+def build(verbose: bool = False) -> str:
+    """Compile every CUDA source for sm_100a and link ``lib/libb200seg.so`` (no GPU needed)."""
+    from torch.utils import cpp_extension
+    os.makedirs(LIB_DIR, exist_ok=True)
+    build_dir = os.path.join(REPO_DIR, "build", "b200seg")
+    os.makedirs(build_dir, exist_ok=True)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0a")
+    os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
+    cpp_extension.load(
+        name="b200seg_C",
+        sources=sources(),
+        extra_include_paths=[os.path.join(REPO_DIR, "include"), CSRC_DIR],
+        extra_cflags=["-O3", "-std=c++17"],
+        extra_cuda_cflags=NVCC_FLAGS,
+        extra_ldflags=[],
+        build_directory=build_dir,
+        is_python_module=False,
+        verbose=verbose,
+    )
+    built = os.path.join(build_dir, "b200seg_C.so")
+    shutil.copy2(built, LIB_PATH)
+    global _tried, _lib_loaded
+    _tried = _lib_loaded is not None
+    return LIB_PATH
+
+
+def library() -> Optional[str]:
+    """Path of the loaded library, loading it on first use; ``None`` if it is not built."""
+    global _lib_loaded, _load_error, _tried
+    if _lib_loaded or _tried:
+        return _lib_loaded
+    _tried = True
+    if not os.path.exists(LIB_PATH):
+        _load_error = f"{LIB_PATH} does not exist"
+        return None
+    try:
+        torch.ops.load_library(LIB_PATH)
+        _lib_loaded = LIB_PATH
+    except Exception as exc:  # pragma: no cover - depends on the box
+        _load_error = f"{type(exc).__name__}: {exc}"
+    return _lib_loaded
+
+
+def load_error() -> Optional[str]:
+    return _load_error

@@ -1,0 +1,172 @@
+"""Gradient exchange: the all-reduce that replaces the reference's gather -> root reduce ->
+broadcast round (``grad_serv_mean`` ``R:255-440`` and ``grad_client_mean`` ``R:443-556``).
+
+One ``GradientSynchronizer`` owns the flat fp32 gradient buffer of a replica and offers
+
+``sync(k_accum) -> grad_scale``
+    make ``flat_grad`` hold the same bits on every rank (reference capability: "bit-identical
+    reduced gradient on every replica", ``R:402-433``) and return the factor the optimizer must
+    still apply (``1/world`` for the mean over ranks, ``1/K`` for the mean over the K accumulated
+    micro-batches; they are folded into the fused optimizer kernel instead of costing a pass).
+
+Back-ends
+---------
+``native``  sm_100a kernels over NVLink peer memory (``csrc/comm``): one-shot for small buffers,
+            two-shot (reduce-scatter + all-gather through peer loads/stores) for large ones,
+            wire format chosen by the codec, dequantize-on-load with fp32 accumulation in fixed
+            rank order.  No NCCL call on this path.
+``torch``   ``torch.distributed`` (NCCL or gloo).  fp32: one ``all_reduce``.  Lossy codecs:
+            quantize locally, ``all_gather`` payloads and scales, dequantize-accumulate in rank
+            order -- same result on every rank, compressed bytes on the wire.
+``star``    the reference's topology over ``parallel.star`` (TCP, msgpack, gzip), for CPU-only
+            clusters and for parity tests: gather to rank 0, reduce, re-encode, broadcast,
+            self-decode (``R:405-432``).
+
+Reduction semantics: ``mean`` is the exact mean over ``world_size`` replicas.
+``sum`` reproduces what the reference computes when it has one worker (server + worker).
+``reference_q1`` reproduces its formula for any worker count (for parity experiments only).
+"""
+from __future__ import annotations
+
+import time
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .codecs import Codec, get_codec
+from .dist import DistContext
+
+
+class GradientSynchronizer:
+    def __init__(self, flat_grad: torch.Tensor, ctx: DistContext, codec: str = "fp32",
+                 reduce: str = "mean", accumulate: str = "mean", backend: str = "auto",
+                 requantize_output: bool = False, star=None, bucket_mb: float = 25.0):
+        self.flat = flat_grad
+        self.ctx = ctx
+        self.codec: Codec = get_codec(codec)
+        self.reduce = reduce
+        self.accumulate = accumulate
+        self.requantize_output = requantize_output
+        self.star = star
+        self.bucket_elems = max(int(bucket_mb * (1 << 20)) // 4, 1)
+        if backend == "auto":
+            backend = "star" if star is not None else "torch"
+            if star is None and flat_grad.is_cuda and ctx.world_size > 1:
+                from . import symm
+                backend = "native" if symm.available(ctx) else "torch"
+        self.backend = backend
+        self.native = None
+        if backend == "native" and ctx.world_size > 1:
+            from . import symm
+            self.native = symm.SymmetricAllReduce(flat_grad, ctx, self.codec)
+            self.flat = self.native.buffer          # gradients now live in symmetric memory
+        self.timings: Dict[str, float] = {}
+        self.bytes_on_wire = 0
+
+    # -------------------------------------------------------------------------------------------
+    def _post_scale(self, k_accum: int) -> float:
+        s = 1.0
+        if self.accumulate == "mean" and k_accum > 1:
+            s /= k_accum
+        if self.reduce == "mean" and self.ctx.world_size > 1:
+            s /= self.ctx.world_size
+        return s
+
+    def sync(self, k_accum: int = 1) -> float:
+        """All-reduce (sum over ranks) in place; returns the scale still to be applied."""
+        t0 = time.perf_counter()
+        world = self.ctx.world_size
+        if world > 1 or self.star is not None:
+            if self.backend == "native":
+                self.native.all_reduce_()
+            elif self.backend == "star":
+                self._sync_star()
+            else:
+                self._sync_torch()
+        elif self.codec.name != "fp32" and self.requantize_output:
+            self._roundtrip_local()
+        self.timings["sync_s"] = time.perf_counter() - t0
+        return self._post_scale(k_accum)
+
+    # -- torch.distributed -------------------------------------------------------------------
+    def _roundtrip_local(self) -> None:
+        payload, scale = self.codec.encode(self.flat)
+        self.codec.decode(payload, scale, out=self.flat)
+
+    def _sync_torch(self) -> None:
+        world = self.ctx.world_size
+        c = self.codec
+        if c.name == "fp32":
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+            self.bytes_on_wire += self.flat.numel() * 4
+        else:
+            payload, scale = c.encode(self.flat)
+            wire = payload.view(torch.uint8)          # raw bytes: every backend moves uint8
+            gathered = [torch.empty_like(wire) for _ in range(world)]
+            scales = [torch.empty_like(scale) for _ in range(world)]
+            dist.all_gather(gathered, wire)
+            dist.all_gather(scales, scale)
+            self.flat.zero_()
+            for r in range(world):                       # fixed order -> identical bits everywhere
+                c.decode(gathered[r].view(payload.dtype), scales[r], out=self.flat,
+                         accumulate=True)
+            self.bytes_on_wire += payload.numel() * c.wire_bytes
+        if self.requantize_output and c.name != "fp32":
+            self._roundtrip_local()
+
+    # -- TCP star (reference topology) -----------------------------------------------------------
+    def _sync_star(self) -> None:
+        c = self.codec
+        star = self.star
+        t = {}
+        t0 = time.perf_counter()
+        payload, scale = c.encode(self.flat)
+        t["encode_s"] = time.perf_counter() - t0                 # R:497
+        if self.ctx.rank != 0:
+            t0 = time.perf_counter()
+            self.bytes_on_wire += star.send({"max": float(scale), "q": payload})   # R:503
+            t["send_s"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            msg = star.recv()                                      # R:512
+            t["recv_s"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            self._decode_into(msg)
+            t["decode_s"] = time.perf_counter() - t0              # R:547
+        else:
+            t0 = time.perf_counter()
+            msgs = star.gather()                                   # R:264
+            t["recv_s"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            if self.reduce == "reference_q1":
+                m = len(msgs)
+                for msg in msgs:                                   # R:288-313 as written
+                    self.flat.div_(m)
+                    w = c.decode(msg["q"].to(self.flat.device),
+                                 torch.tensor(msg["max"], device=self.flat.device))
+                    self.flat.add_(w.view_as(self.flat), alpha=1.0 / m)
+            else:
+                own_q = payload.clone() if payload.data_ptr() == self.flat.data_ptr() else payload
+                own_s = scale
+                self.flat.zero_()
+                c.decode(own_q, own_s, out=self.flat, accumulate=True)
+                for msg in msgs:
+                    c.decode(msg["q"].to(self.flat.device).view(-1),
+                             torch.tensor(msg["max"], dtype=torch.float32, device=self.flat.device),
+                             out=self.flat, accumulate=True)
+            t["reduce_s"] = time.perf_counter() - t0              # R:322
+            t0 = time.perf_counter()
+            out_q, out_s = c.encode(self.flat)                      # R:367-387
+            t["requantize_s"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            self.bytes_on_wire += star.broadcast({"max": float(out_s), "q": out_q})   # R:396
+            t["send_s"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            c.decode(out_q, out_s, out=self.flat)                   # self-decode, R:405-432
+            t["decode_s"] = time.perf_counter() - t0
+        self.timings.update(t)
+
+    def _decode_into(self, msg) -> None:
+        q = msg["q"].to(self.flat.device).view(-1)
+        s = torch.tensor(msg["max"], dtype=torch.float32, device=self.flat.device)
+        self.codec.decode(q, s, out=self.flat)

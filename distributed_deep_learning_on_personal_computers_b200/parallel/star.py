@@ -1,0 +1,253 @@
+"""TCP-star compatibility transport: the reference's wire path, made safe.
+
+The reference moves everything through blocking TCP sockets in a star around rank 0
+(``R:173-220``): each message is ``pickle`` -> (optional) multi-threaded gzip level 1
+(``parallel_compress`` / ``parallel_decompress``, ``R:43-69``) -> 4-byte big-endian length prefix ->
+payload (``R:119-120``, ``R:75-102``).  Collectives are "send to every worker in turn" and "receive
+from every worker in turn" (``R:210-220``).  On NVLink none of this is on the hot path (see
+``parallel.allreduce``); it exists for capability parity and for CPU-only clusters, and is what
+BASELINE config 1 style runs can use with ``comm="star"``.
+
+Differences, all deliberate:
+
+* no ``pickle``: messages are msgpack maps of scalars, strings and raw tensor bytes, so a peer
+  cannot make us execute code;
+* same framing (``>I`` length prefix) but ``recv`` collects into a pre-sized ``bytearray``
+  (the reference's ``data += packet`` is quadratic, SURVEY 3.4 hot loop 3);
+* deflate stage = standard multi-member gzip produced block-parallel by a thread pool
+  (zlib releases the GIL); ``mgzip`` output is the same format, so either side can read the other;
+* timeouts, connect retries, and a ``PeerLost`` exception on EOF instead of ``None`` flowing
+  into ``len()``;
+* address and port come from the config / environment, never from a table in the source (Q17).
+"""
+from __future__ import annotations
+
+import gzip
+import socket
+import struct
+import time
+import zlib
+from concurrent.futures import ThreadPoolExecutor
+from typing import Any, Dict, List, Optional, Sequence
+
+import msgpack
+import numpy as np
+import torch
+
+_LEN = struct.Struct(">I")          # R:119
+MAX_MESSAGE = (1 << 32) - 1
+
+
+class PeerLost(ConnectionError):
+    """The other side closed the connection or stopped answering."""
+
+
+# ---- lossless stage (C2) ---------------------------------------------------------------------
+def deflate(data: bytes, level: int = 1, threads: int = 12, block: int = 1_000_000) -> bytes:
+    """Multi-member gzip, one member per ``block`` bytes, compressed in parallel (R:51)."""
+    if len(data) <= block or threads <= 1:
+        return gzip.compress(data, compresslevel=level, mtime=0)
+    chunks = [data[i:i + block] for i in range(0, len(data), block)]
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        parts = list(pool.map(lambda c: gzip.compress(c, compresslevel=level, mtime=0), chunks))
+    return b"".join(parts)
+
+
+def inflate(data: bytes) -> bytes:
+    """Inverse of ``deflate``; also reads ``mgzip`` output (ordinary multi-member gzip)."""
+    out = []
+    while data:
+        d = zlib.decompressobj(wbits=31)
+        out.append(d.decompress(data))
+        out.append(d.flush())
+        data = d.unused_data
+    return b"".join(out)
+
+
+# ---- message codec ---------------------------------------------------------------------------
+_NP_OF = {torch.float32: np.float32, torch.float16: np.float16, torch.int8: np.int8,
+          torch.uint8: np.uint8, torch.int64: np.int64, torch.float64: np.float64,
+          torch.int32: np.int32, torch.bool: np.bool_}
+
+
+def tensor_to_wire(t: torch.Tensor) -> Dict[str, Any]:
+    t = t.detach().cpu().contiguous()
+    if t.dtype == torch.bfloat16 or "float8" in str(t.dtype):
+        raw = t.view(torch.uint8 if t.element_size() == 1 else torch.int16).numpy().tobytes()
+    else:
+        raw = t.numpy().tobytes()
+    return {"__t__": str(t.dtype).replace("torch.", ""), "s": list(t.shape), "b": raw}
+
+
+def tensor_from_wire(d: Dict[str, Any]) -> torch.Tensor:
+    dtype = getattr(torch, d["__t__"])
+    if dtype == torch.bfloat16:
+        a = np.frombuffer(d["b"], dtype=np.int16).copy()
+        return torch.from_numpy(a).view(torch.bfloat16).reshape(d["s"])
+    if "float8" in d["__t__"]:
+        a = np.frombuffer(d["b"], dtype=np.uint8).copy()
+        return torch.from_numpy(a).view(dtype).reshape(d["s"])
+    a = np.frombuffer(d["b"], dtype=_NP_OF[dtype]).copy()
+    return torch.from_numpy(a).reshape(d["s"])
+
+
+def _pack_default(o):
+    if isinstance(o, torch.Tensor):
+        return tensor_to_wire(o)
+    if isinstance(o, (np.floating, np.integer)):
+        return o.item()
+    raise TypeError(f"cannot serialise {type(o)}")
+
+
+def _unpack_hook(d):
+    return tensor_from_wire(d) if "__t__" in d else d
+
+
+def pack(obj: Any, compress: bool = True, level: int = 1, threads: int = 12,
+         block: int = 1_000_000) -> bytes:
+    raw = msgpack.packb(obj, default=_pack_default, use_bin_type=True)
+    return deflate(raw, level, threads, block) if compress else raw
+
+
+def unpack(data: bytes, compressed: bool = True) -> Any:
+    raw = inflate(data) if compressed else data
+    return msgpack.unpackb(raw, object_hook=_unpack_hook, raw=False, strict_map_key=False)
+
+
+# ---- framing (C3) ---------------------------------------------------------------------------
+def send_frame(sock: socket.socket, payload: bytes) -> None:
+    if len(payload) > MAX_MESSAGE:
+        raise ValueError("message exceeds the 4 GiB-1 frame limit of the >I length prefix")
+    try:
+        sock.sendall(_LEN.pack(len(payload)) + payload)
+    except (BrokenPipeError, ConnectionResetError, socket.timeout) as exc:
+        raise PeerLost(f"send failed: {exc}") from exc
+
+
+def _recv_exact(sock: socket.socket, n: int) -> bytes:
+    buf = bytearray(n)
+    view = memoryview(buf)
+    got = 0
+    while got < n:
+        try:
+            k = sock.recv_into(view[got:], n - got)
+        except socket.timeout as exc:
+            raise PeerLost(f"timed out after {got}/{n} bytes") from exc
+        except ConnectionResetError as exc:
+            raise PeerLost(str(exc)) from exc
+        if k == 0:
+            raise PeerLost(f"peer closed the connection after {got}/{n} bytes")
+        got += k
+    return bytes(buf)
+
+
+def recv_frame(sock: socket.socket) -> bytes:
+    (n,) = _LEN.unpack(_recv_exact(sock, _LEN.size))
+    return _recv_exact(sock, n)
+
+
+# ---- endpoints (C4-C8) -----------------------------------------------------------------------
+class _Endpoint:
+    def __init__(self, compress=True, level=1, threads=12, block=1_000_000):
+        self.compress, self.level, self.threads, self.block = compress, level, threads, block
+        self.bytes_sent = 0
+        self.bytes_received = 0
+        self.last_raw_bytes = 0
+
+    def _send(self, sock, obj):
+        payload = pack(obj, self.compress, self.level, self.threads, self.block)
+        self.bytes_sent += len(payload)
+        send_frame(sock, payload)
+        return len(payload)
+
+    def _recv(self, sock):
+        payload = recv_frame(sock)
+        self.bytes_received += len(payload)
+        return unpack(payload, self.compress)
+
+
+class StarServer(_Endpoint):
+    """Rank 0: accepts ``n_workers`` connections, then broadcasts / gathers (R:173-191, R:210-220).
+
+    Workers announce their rank in a hello message, so the reduction order is the rank order
+    rather than the accept order of the reference (deterministic across runs).
+    """
+
+    def __init__(self, addr: str, port: int, n_workers: int, timeout: float = 600.0, **kw):
+        super().__init__(**kw)
+        self.listener = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+        self.listener.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        self.listener.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)     # R:175
+        self.listener.bind((addr, port))
+        self.listener.listen(max(n_workers, 1))
+        self.listener.settimeout(timeout)
+        self.port = self.listener.getsockname()[1]
+        self.n_workers = n_workers
+        self.timeout = timeout
+        self.conns: List[socket.socket] = []
+
+    def accept_all(self) -> None:
+        pending = {}
+        while len(pending) < self.n_workers:
+            try:
+                conn, _ = self.listener.accept()
+            except socket.timeout as exc:
+                raise PeerLost(f"only {len(pending)}/{self.n_workers} workers joined") from exc
+            conn.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+            conn.settimeout(self.timeout)
+            hello = unpack(recv_frame(conn), compressed=False)
+            pending[int(hello["rank"])] = conn
+        self.conns = [pending[r] for r in sorted(pending)]
+
+    def broadcast(self, obj: Any) -> int:
+        """Pack once, send to every worker (the reference re-packs per worker)."""
+        payload = pack(obj, self.compress, self.level, self.threads, self.block)
+        for c in self.conns:
+            send_frame(c, payload)
+        self.bytes_sent += len(payload) * len(self.conns)
+        return len(payload)
+
+    def gather(self) -> List[Any]:
+        return [self._recv(c) for c in self.conns]
+
+    def close(self) -> None:
+        for c in self.conns:
+            try:
+                c.close()
+            except OSError:
+                pass
+        self.listener.close()
+
+
+class StarWorker(_Endpoint):
+    """Rank > 0: connects to the server, with retries (R:194-206 has none)."""
+
+    def __init__(self, addr: str, port: int, rank: int, timeout: float = 600.0,
+                 connect_retries: int = 200, retry_delay: float = 0.05, **kw):
+        super().__init__(**kw)
+        last: Optional[Exception] = None
+        self.sock = None
+        for _ in range(connect_retries):
+            s = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+            s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)              # R:200
+            s.settimeout(timeout)
+            try:
+                s.connect((addr, port))
+                self.sock = s
+                break
+            except (ConnectionRefusedError, socket.timeout, OSError) as exc:
+                last = exc
+                s.close()
+                time.sleep(retry_delay)
+        if self.sock is None:
+            raise PeerLost(f"could not reach the server at {addr}:{port}: {last}")
+        send_frame(self.sock, pack({"rank": rank}, compress=False))
+
+    def send(self, obj: Any) -> int:
+        return self._send(self.sock, obj)
+
+    def recv(self) -> Any:
+        return self._recv(self.sock)
+
+    def close(self) -> None:
+        self.sock.close()

@@ -1,0 +1,329 @@
+"""The training loop: micro-batches, local accumulation, gradient exchange, replicated step.
+
+This is the B200-first re-statement of the reference's server / worker main programs
+(``R:690-790`` and ``R:792-895``; ``R`` = the reference script).  What is kept:
+
+* every rank holds a full replica and the same optimizer (``R:702-704``, ``R:810``);
+* rank 0 is the coordinator: it provides the initial state (``R:708``), owns the run log
+  (``R:715-716``, ``R:781-782``) and the sample images (``R:785-790``);
+* micro-batches of ``batch_size`` tiles, gradients accumulated locally, exchanged every
+  ``sync_every`` micro-batches (``R:685``, ``R:756-763``), then ``optimizer.step()`` on every rank
+  with bit-identical gradients (``R:437``, ``R:552``);
+* per-epoch mean loss / pixel accuracy and timings (``R:765-782``).
+
+What is different (SURVEY 0.3 decides each quirk): ranks see disjoint shards (Q2); the reduction
+is an exact mean (Q1) unless ``reduce="sum"``; accumulated micro-batches are averaged (Q8) unless
+``accumulate="sum"``; the tail of an epoch is flushed instead of leaking into the next (Q7);
+evaluation runs in ``eval()`` mode on the hold-out split the reference cuts off and never uses
+(Q9); data is loaded once (Q12); per-step time is device time (Q13).
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Dict, Optional
+
+import torch
+
+from .config import TrainConfig
+from .models.unet import UNet, count_parameters
+from .models.engine import NativeEngine
+from .ops import functional as Fn
+from .optim import build_optimizer
+from .parallel import dist as pdist
+from .parallel.allreduce import GradientSynchronizer
+from .utils import checkpoint as ckpt
+from .utils.data import PinnedBatchLoader, RankSampler, TileSet, build_datasets
+from .utils.metrics import DeviceMeter, RunLog, dump_samples
+from .utils.timing import PhaseTimer
+
+
+class Trainer:
+    def __init__(self, cfg: TrainConfig, ctx: Optional[pdist.DistContext] = None,
+                 datasets=None):
+        self.cfg = cfg
+        self.ctx = ctx or pdist.init(cfg)
+        cfg.rank, cfg.world_size = self.ctx.rank, self.ctx.world_size
+        dev = self.ctx.device
+        self.device = dev
+        torch.manual_seed(cfg.seed)                       # same seed: ranks agree before broadcast
+        self.model = UNet(cfg.out_classes, cfg.up_sample_mode, cfg.base_channels, cfg.in_channels)
+        self.model.to(dev)
+        self.model.flatten_parameters(dev)
+        pdist.broadcast_model_state(self.model, self.ctx)   # rank 0 -> all (R:560-565)
+
+        self.star = None
+        comm = cfg.comm
+        if comm == "star" and cfg.world_size > 1:
+            self.star = self._open_star()
+        self.sync = GradientSynchronizer(
+            self.model.flat["grad"], self.ctx, codec=cfg.codec, reduce=cfg.reduce,
+            accumulate=cfg.accumulate, backend=("auto" if comm == "auto" else comm),
+            requantize_output=cfg.requantize_output, star=self.star, bucket_mb=cfg.bucket_mb)
+        if self.sync.flat is not self.model.flat["grad"]:
+            self._rebind_grad(self.sync.flat)
+
+        self.engine_kind = cfg.engine if cfg.engine != "auto" else "native"
+        self.engine: Optional[NativeEngine] = None
+        self._engine_shape = None
+        self.optimizer = build_optimizer(self.model, cfg)
+        self.optimizer.rebind_grad(self.model.flat["grad"])
+
+        self.train_set, self.hold_set = datasets if datasets is not None else build_datasets(cfg)
+        self.sampler = RankSampler(len(self.train_set), self.ctx.rank, self.ctx.world_size,
+                                   cfg.shuffle, cfg.shard_data, cfg.seed)
+        self.loader = PinnedBatchLoader(self.train_set, cfg.batch_size, dev)
+        self.log = RunLog(cfg, enabled=self.ctx.is_coordinator)
+        self.timer = PhaseTimer(dev)
+        self.meter = DeviceMeter(dev)
+        self.epoch = 0
+        self.global_step = 0          # micro-batches seen
+        self.pending = 0              # micro-batches accumulated since the last exchange
+        self._graph = None
+        self._graph_launches = 0
+        if cfg.resume:
+            self.resume(cfg.resume)
+
+    # -- plumbing ----------------------------------------------------------------------------------
+    def _open_star(self):
+        from .parallel import star
+        kw = dict(compress=self.cfg.compress, level=self.cfg.compress_level,
+                  threads=self.cfg.compress_threads, block=self.cfg.compress_block)
+        port = self.cfg.master_port + 1
+        if self.ctx.rank == 0:
+            srv = star.StarServer(self.cfg.master_addr, port, self.ctx.world_size - 1,
+                                  self.cfg.timeout_s, **kw)
+            srv.accept_all()
+            return _StarFacade(srv)
+        return _StarFacade(star.StarWorker(self.cfg.master_addr, port, self.ctx.rank,
+                                           self.cfg.timeout_s, **kw))
+
+    def _rebind_grad(self, new_flat: torch.Tensor) -> None:
+        """Point every ``.grad`` view (and the engine / optimizer) at ``new_flat``."""
+        m = self.model
+        convT = {n for n, mod in m.named_modules() if isinstance(mod, torch.nn.ConvTranspose2d)}
+        new_flat.zero_()
+        for name, p in m.named_parameters():
+            off, _ = m.flat["offsets"][name]
+            is_t = name.rsplit(".", 1)[0] in convT and p.dim() == 4
+            p.grad = UNet._internal_view(new_flat, off, p, is_t)
+        m.flat["grad"] = new_flat
+
+    def _ensure_engine(self, n: int, h: int, w: int) -> NativeEngine:
+        if self.engine is None or self._engine_shape != (n, h, w):
+            self.engine = NativeEngine(self.model, n, h, w)
+            self._engine_shape = (n, h, w)
+            self.optimizer.attach_lowp(self.engine.flat_lp)
+            self._graph = None
+        return self.engine
+
+    # -- one micro-batch ---------------------------------------------------------------------------
+    def micro_step(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> torch.Tensor:
+        """Forward + loss + backward; gradients accumulate. Returns device ``[loss_sum, correct]``."""
+        n, h, w, _ = images_u8.shape
+        if self.engine_kind == "torch":
+            return self._micro_step_autograd(images_u8, labels_u8)
+        eng = self._ensure_engine(n, h, w)
+        eng.load_batch(images_u8, labels_u8)
+        use_graph = self.cfg.cuda_graph and self.device.type == "cuda"
+        if not use_graph:
+            return eng.train_microbatch()
+        if self._graph is None:
+            # warm-up on a side stream (allocator, lazy module loads), then capture once
+            s = torch.cuda.Stream(self.device)
+            s.wait_stream(torch.cuda.current_stream(self.device))
+            saved = self.model.flat["grad"].clone()
+            bufs = [b.clone() for b in self.model.buffers()]
+            with torch.cuda.stream(s):
+                eng.train_microbatch()
+            torch.cuda.current_stream(self.device).wait_stream(s)
+            self.model.flat["grad"].copy_(saved)                 # undo the warm-up's side effects
+            for b, keep in zip(self.model.buffers(), bufs):
+                b.copy_(keep)
+            before = Fn.launch_count()
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                eng.train_microbatch()
+            self._graph_launches = Fn.launch_count() - before
+            self.model.flat["grad"].copy_(saved)
+            for b, keep in zip(self.model.buffers(), bufs):
+                b.copy_(keep)
+            Fn._tick(-self._graph_launches)
+        self._graph.replay()
+        Fn._tick(self._graph_launches)
+        return eng.loss_acc
+
+    def _micro_step_autograd(self, images_u8, labels_u8) -> torch.Tensor:
+        """Stock-PyTorch path (eager autograd, as the reference's R:754-756), for comparison."""
+        x = (images_u8.float() / 255.0).permute(0, 3, 1, 2)
+        y = labels_u8.long()
+        amp = self.device.type == "cuda" and self.cfg.dtype in ("auto", "bf16")
+        if amp:
+            x = x.contiguous(memory_format=torch.channels_last)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+            logits = self.model(x)
+        loss = torch.nn.functional.cross_entropy(logits.float(), y)
+        loss.backward()
+        with torch.no_grad():
+            px = y.numel()
+            correct = (logits.argmax(1) == y).sum()
+            return torch.stack([loss.detach() * px, correct.float()])
+
+    # -- exchange + step --------------------------------------------------------------------------
+    def sync_and_step(self) -> None:
+        k = max(self.pending, 1)
+        with self.timer.phase("sync"):
+            scale = self.sync.sync(k)
+        with self.timer.phase("optimizer"):
+            self.optimizer.step(grad_scale=scale, zero_grad=True)
+            if self.engine is not None and self.optimizer.p_lowp is None:
+                self.engine.refresh_lowp()
+        self.pending = 0
+
+    # -- epochs --------------------------------------------------------------------------------------
+    def train_epoch(self) -> Dict[str, float]:
+        cfg = self.cfg
+        t_epoch = time.perf_counter()
+        self.meter.reset()
+        self.timer.reset()
+        order = self.sampler.indices(self.epoch)
+        it = 0
+        for images, labels in self.loader.batches(order):
+            with self.timer.phase("micro_batch"):
+                out = self.micro_step(images, labels)
+            self.meter.add(out, labels.numel())
+            it += 1
+            self.pending += 1
+            self.global_step += 1
+            if it % cfg.sync_every == 0:                           # R:759
+                self.sync_and_step()
+            if cfg.max_steps and self.global_step >= cfg.max_steps:
+                break
+        if self.pending and cfg.flush_at_epoch_end:                 # Q7
+            self.sync_and_step()
+        stats = self.meter.read()
+        tm = self.timer.summary()
+        stats.update(epoch=self.epoch, epoch_s=time.perf_counter() - t_epoch,
+                     step_ms=tm.get("micro_batch", 0.0), sync_ms=tm.get("sync", 0.0),
+                     optimizer_ms=tm.get("optimizer", 0.0), micro_batches=it)
+        if self.device.type == "cuda":
+            stats["tiles_per_s"] = cfg.batch_size * 1e3 / max(stats["step_ms"], 1e-9)
+        return stats
+
+    @torch.no_grad()
+    def evaluate(self, tiles: Optional[TileSet] = None, limit: Optional[int] = None) -> Dict[str, float]:
+        """Loss / pixel accuracy in eval mode (running BN statistics) on a tile set."""
+        tiles = tiles if tiles is not None else self.hold_set
+        if tiles is None or len(tiles) == 0:
+            return {}
+        n = len(tiles) if limit is None else min(limit, len(tiles))
+        b = self.cfg.batch_size
+        meter = DeviceMeter(self.device)
+        was_training = self.model.training
+        self.model.eval()
+        for i in range(0, n - b + 1, b):
+            img = tiles.images[i:i + b].to(self.device)
+            lab = tiles.labels[i:i + b].to(self.device)
+            if self.engine_kind == "torch":
+                x = (img.float() / 255.0).permute(0, 3, 1, 2)
+                logits = self.model(x)
+                loss = torch.nn.functional.cross_entropy(logits.float(), lab.long(), reduction="sum")
+                out = torch.stack([loss, (logits.argmax(1) == lab.long()).sum().float()])
+            else:
+                eng = self._ensure_engine(*img.shape[:3])
+                eng.load_batch(img, lab)
+                out = eng.evaluate()
+            meter.add(out, lab.numel())
+        self.model.train(was_training)
+        r = meter.read()
+        return {"eval_loss": r["mean_loss"], "eval_accuracy": r["mean_accuracy"]}
+
+    @torch.no_grad()
+    def predict(self, images_u8: torch.Tensor) -> torch.Tensor:
+        """Arg-max class map (uint8, N x H x W) for uint8 NHWC tiles, eval mode."""
+        img = images_u8.to(self.device)
+        if self.engine_kind == "torch":
+            self.model.eval()
+            out = self.model((img.float() / 255.0).permute(0, 3, 1, 2)).argmax(1).to(torch.uint8)
+            self.model.train()
+            return out
+        preds = []
+        b = self.cfg.batch_size
+        for i in range(0, img.shape[0], b):
+            chunk = img[i:i + b]
+            pad = b - chunk.shape[0]
+            if pad:
+                chunk = torch.cat([chunk, chunk[-1:].expand(pad, -1, -1, -1)])
+            eng = self._ensure_engine(*chunk.shape[:3])
+            eng.load_batch(chunk, torch.zeros(chunk.shape[:3], dtype=torch.uint8, device=self.device))
+            eng.evaluate()
+            preds.append(eng.pred[:b - pad].clone())
+        return torch.cat(preds)
+
+    def dump_samples(self) -> None:
+        k = min(self.cfg.sample_images, len(self.train_set))
+        if not self.ctx.is_coordinator or k == 0:
+            return
+        imgs = self.train_set.images[:k]
+        preds = self.predict(imgs)
+        dump_samples(os.path.join(self.cfg.out_dir, "samples"), imgs, self.train_set.labels[:k], preds)
+
+    def fit(self) -> Dict[str, float]:
+        cfg = self.cfg
+        self.log.header(count_parameters(self.model), resumed=bool(cfg.resume))
+        last: Dict[str, float] = {}
+        while self.epoch < cfg.epochs:
+            last = self.train_epoch()
+            if cfg.eval_holdout and self.hold_set is not None:
+                last.update(self.evaluate())
+            self.log.epoch(self.epoch, last["mean_loss"], last["mean_accuracy"], last["epoch_s"],
+                           last["step_ms"], last["sync_ms"],
+                           {k: v for k, v in last.items() if k.startswith(("eval_", "tiles_"))})
+            if cfg.sample_images:
+                self.dump_samples()
+            self.epoch += 1
+            if self.ctx.is_coordinator and cfg.save_every_epochs and \
+                    self.epoch % cfg.save_every_epochs == 0:
+                self.save(os.path.join(cfg.out_dir, "checkpoint.pt"))
+            self.ctx.barrier()
+            if cfg.max_steps and self.global_step >= cfg.max_steps:
+                break
+        return last
+
+    # -- checkpoint --------------------------------------------------------------------------------
+    def save(self, path: str) -> str:
+        return ckpt.save(path, self.model, self.optimizer, self.epoch, self.global_step,
+                         self.cfg.to_dict())
+
+    def resume(self, path: str) -> None:
+        state = ckpt.load(path, self.model, self.optimizer)
+        self.epoch, self.global_step = state["epoch"], state["step"]
+        if self.engine is not None:
+            self.engine.refresh_lowp()
+
+    def close(self) -> None:
+        if self.star is not None:
+            self.star.close()
+        self.ctx.shutdown()
+
+
+class _StarFacade:
+    """Gives server and worker endpoints the one interface ``GradientSynchronizer`` uses."""
+
+    def __init__(self, endpoint):
+        self.ep = endpoint
+
+    def send(self, obj):
+        return self.ep.send(obj)
+
+    def recv(self):
+        return self.ep.recv()
+
+    def gather(self):
+        return self.ep.gather()
+
+    def broadcast(self, obj):
+        return self.ep.broadcast(obj)
+
+    def close(self):
+        self.ep.close()
