@@ -1,0 +1,264 @@
+// torch.ops.b200seg.* : thin tensor-checking wrappers over the C ABI in include/b200seg.h.
+// All launches go to the current CUDA stream, so they are capturable in CUDA graphs.
+#include <torch/library.h>
+#include <ATen/ATen.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <optional>
+#include <string>
+#include <map>
+#include "b200seg.h"
+
+namespace {
+
+using at::Tensor;
+using OptT = std::optional<Tensor>;
+
+inline cudaStream_t cur() { return at::cuda::getCurrentCUDAStream(); }
+
+inline void ok(int err, const char* what) {
+  TORCH_CHECK(err == 0, "b200seg::", what, " failed: ", cudaGetErrorString((cudaError_t)err));
+}
+
+// (N,H,W,C) view with contiguous channels and "dense pixels": returns the pixel stride.
+inline int64_t nhwc_ld(const Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda() && t.dim() == 4, name, ": expected a CUDA (N,H,W,C) tensor");
+  TORCH_CHECK(t.stride(3) == 1, name, ": channels must be contiguous");
+  const int64_t ld = t.stride(2);
+  TORCH_CHECK(t.stride(1) == ld * t.size(2) && t.stride(0) == ld * t.size(2) * t.size(1), name,
+              ": pixels must be densely strided");
+  TORCH_CHECK(ld % 8 == 0 && (reinterpret_cast<uintptr_t>(t.data_ptr()) % 16) == 0, name,
+              ": needs 16-byte aligned pixels");
+  return ld;
+}
+inline void* ptr_or_null(const OptT& t) { return t.has_value() ? t->data_ptr() : nullptr; }
+inline float* f32(const Tensor& t) {
+  TORCH_CHECK(t.scalar_type() == at::kFloat && t.is_cuda(), "expected a CUDA float32 tensor");
+  return t.data_ptr<float>();
+}
+inline void bf16(const Tensor& t, const char* n) {
+  TORCH_CHECK(t.scalar_type() == at::kBFloat16, n, ": expected bfloat16");
+}
+
+int64_t stats_rows() { return b200seg_stats_rows(); }
+
+void channel_stats(const Tensor& y, Tensor partial) {
+  c10::cuda::CUDAGuard g(y.device());
+  bf16(y, "y");
+  int64_t ld = nhwc_ld(y, "y");
+  ok(b200seg_channel_stats(y.data_ptr(), y.size(0) * y.size(1) * y.size(2), (int)y.size(3), ld, f32(partial),
+                           (int)partial.size(0), cur()), "channel_stats");
+}
+
+void bn_finalize(const OptT& partial, int64_t count, const Tensor& gamma, const Tensor& beta,
+                 const Tensor& rmean, const Tensor& rvar, const Tensor& nbt, Tensor ss, double momentum,
+                 double eps, bool training) {
+  c10::cuda::CUDAGuard g(ss.device());
+  const int C = (int)gamma.numel();
+  TORCH_CHECK(!training || partial.has_value(), "training-mode bn_finalize needs the partial sums");
+  TORCH_CHECK(nbt.scalar_type() == at::kLong, "num_batches_tracked must be int64");
+  ok(b200seg_bn_finalize(partial.has_value() ? f32(*partial) : nullptr,
+                         partial.has_value() ? (int)partial->size(0) : 0, count, f32(gamma), f32(beta),
+                         f32(rmean), f32(rvar), (long long*)nbt.data_ptr<int64_t>(), f32(ss), C,
+                         (float)momentum, (float)eps, training ? 1 : 0, cur()), "bn_finalize");
+}
+
+void bn_relu_pool_fwd(const Tensor& y, const Tensor& ss, Tensor out, OptT pool) {
+  c10::cuda::CUDAGuard g(y.device());
+  bf16(y, "y"); bf16(out, "out");
+  int64_t ldy = nhwc_ld(y, "y"), ldo = nhwc_ld(out, "out"), ldp = 0;
+  if (pool.has_value()) { bf16(*pool, "pool"); ldp = nhwc_ld(*pool, "pool"); }
+  ok(b200seg_bn_relu_pool_fwd(y.data_ptr(), ldy, f32(ss), out.data_ptr(), ldo, ptr_or_null(pool), ldp,
+                              (int)y.size(0), (int)y.size(1), (int)y.size(2), (int)y.size(3), cur()),
+     "bn_relu_pool_fwd");
+}
+
+void bn_relu_pool_bwd(const OptT& d_out, const OptT& d_pool, const Tensor& y, const Tensor& ss,
+                      const Tensor& gamma, Tensor dgamma, Tensor dbeta, const OptT& dbias, Tensor dy) {
+  c10::cuda::CUDAGuard g(y.device());
+  (void)dbias;   // a conv bias that feeds a train-mode BN has an exactly zero gradient
+  bf16(y, "y"); bf16(dy, "dy");
+  const int C = (int)y.size(3);
+  int64_t ld_do = 0, ld_dp = 0;
+  if (d_out.has_value()) { bf16(*d_out, "d_out"); ld_do = nhwc_ld(*d_out, "d_out"); }
+  if (d_pool.has_value()) { bf16(*d_pool, "d_pool"); ld_dp = nhwc_ld(*d_pool, "d_pool"); }
+  auto ws = at::empty({(int64_t)b200seg_stats_rows() * 2 * C + 3 * C}, y.options().dtype(at::kFloat));
+  ok(b200seg_bn_relu_pool_bwd(ptr_or_null(d_out), ld_do, ptr_or_null(d_pool), ld_dp, y.data_ptr(),
+                              nhwc_ld(y, "y"), f32(ss), f32(gamma), f32(dgamma), f32(dbeta), dy.data_ptr(),
+                              nhwc_ld(dy, "dy"), (int)y.size(0), (int)y.size(1), (int)y.size(2), C,
+                              d_pool.has_value() ? 1 : 0, ws.data_ptr<float>(), cur()),
+     "bn_relu_pool_bwd");
+}
+
+// One zeroed workspace per (device, size) for the head kernel's CTA partials + counter.
+Tensor& head_workspace(const Tensor& like, int64_t bytes) {
+  static std::map<std::pair<int, int64_t>, Tensor> cache;
+  auto key = std::make_pair((int)like.get_device(), bytes);
+  auto it = cache.find(key);
+  if (it == cache.end()) {
+    it = cache.emplace(key, at::zeros({bytes}, like.options().dtype(at::kByte))).first;
+  }
+  return it->second;
+}
+
+void head_ce_fwd_bwd(const Tensor& a, const Tensor& w, const Tensor& b, const Tensor& labels,
+                     double grad_scale, OptT da, OptT dw, OptT db, OptT pred, Tensor loss_acc) {
+  c10::cuda::CUDAGuard g(a.device());
+  bf16(a, "a");
+  const int C = (int)a.size(3), K = (int)w.size(0);
+  TORCH_CHECK(w.size(1) == C && w.is_contiguous(), "head weight must be (classes, C) contiguous");
+  TORCH_CHECK(labels.scalar_type() == at::kByte && labels.is_contiguous(), "labels must be uint8");
+  int64_t ld_da = 0;
+  if (da.has_value()) { bf16(*da, "da"); ld_da = nhwc_ld(*da, "da"); }
+  Tensor& ws = head_workspace(a, b200seg_head_ce_workspace_bytes(C, K));
+  ok(b200seg_head_ce(a.data_ptr(), nhwc_ld(a, "a"), f32(w), f32(b), labels.data_ptr<uint8_t>(),
+                     a.size(0) * a.size(1) * a.size(2), C, K, (float)grad_scale, ptr_or_null(da), ld_da,
+                     dw.has_value() ? f32(*dw) : nullptr, db.has_value() ? f32(*db) : nullptr,
+                     pred.has_value() ? pred->data_ptr<uint8_t>() : nullptr, f32(loss_acc), ws.data_ptr(),
+                     cur()), "head_ce");
+}
+
+void fused_adam(Tensor p, Tensor gr, Tensor m, Tensor v, double lr, double b1, double b2, double eps,
+                double wd, double gscale, double bc1, double bc2, OptT p_lowp, bool zero_grad) {
+  c10::cuda::CUDAGuard g(p.device());
+  if (p_lowp.has_value()) bf16(*p_lowp, "p_lowp");
+  ok(b200seg_fused_adam(f32(p), f32(gr), f32(m), f32(v), p.numel(), (float)lr, (float)b1, (float)b2,
+                        (float)eps, (float)wd, (float)gscale, (float)bc1, (float)bc2, ptr_or_null(p_lowp),
+                        zero_grad ? 1 : 0, cur()), "fused_adam");
+}
+
+void fused_sgd(Tensor p, Tensor gr, OptT buf, double lr, double momentum, double wd, double gscale,
+               OptT p_lowp, bool zero_grad, bool first_step) {
+  c10::cuda::CUDAGuard g(p.device());
+  ok(b200seg_fused_sgd(f32(p), f32(gr), buf.has_value() ? f32(*buf) : nullptr, p.numel(), (float)lr,
+                       (float)momentum, (float)wd, (float)gscale, ptr_or_null(p_lowp), zero_grad ? 1 : 0,
+                       first_step ? 1 : 0, cur()), "fused_sgd");
+}
+
+int codec_id(const std::string& name) {
+  static const char* names[] = {"fp32", "bf16", "fp16", "q201", "q21", "int8s", "fp8"};
+  for (int i = 0; i < 7; ++i) if (name == names[i]) return i;
+  TORCH_CHECK(false, "unknown codec ", name);
+  return -1;
+}
+
+void amax(const Tensor& x, Tensor out) {
+  c10::cuda::CUDAGuard g(x.device());
+  ok(b200seg_amax(f32(x), x.numel(), f32(out), cur()), "amax");
+}
+void codec_encode(const Tensor& x, const Tensor& scale, Tensor out_bytes, std::string codec) {
+  c10::cuda::CUDAGuard g(x.device());
+  ok(b200seg_codec_encode(f32(x), x.numel(), f32(scale), codec_id(codec), out_bytes.data_ptr(), cur()),
+     "codec_encode");
+}
+void codec_decode(const Tensor& in_bytes, const Tensor& scale, Tensor out, std::string codec,
+                  bool accumulate) {
+  c10::cuda::CUDAGuard g(out.device());
+  const int id = codec_id(codec);
+  if (id == 0) {
+    auto src = at::from_blob(in_bytes.data_ptr(), {out.numel()}, out.options());
+    if (accumulate) out.add_(src); else out.copy_(src);
+    return;
+  }
+  ok(b200seg_codec_decode(in_bytes.data_ptr(), out.numel(), f32(scale), id, f32(out), accumulate ? 1 : 0,
+                          cur()), "codec_decode");
+}
+
+void prep_input(const Tensor& img, Tensor out) {
+  c10::cuda::CUDAGuard g(out.device());
+  TORCH_CHECK(img.scalar_type() == at::kByte && img.is_contiguous() && out.is_contiguous(), "prep_input");
+  bf16(out, "out");
+  ok(b200seg_prep_input(img.data_ptr<uint8_t>(), img.numel() / img.size(-1), (int)img.size(-1), out.data_ptr(),
+                        (int)out.size(-1), cur()), "prep_input");
+}
+void upsample_fwd(const Tensor& x, Tensor out) {
+  c10::cuda::CUDAGuard g(x.device());
+  bf16(x, "x"); bf16(out, "out");
+  ok(b200seg_upsample2x_fwd(x.data_ptr(), nhwc_ld(x, "x"), out.data_ptr(), nhwc_ld(out, "out"), (int)x.size(0),
+                            (int)x.size(1), (int)x.size(2), (int)x.size(3), cur()), "upsample2x_fwd");
+}
+void upsample_bwd(const Tensor& gup, Tensor dx) {
+  c10::cuda::CUDAGuard g(dx.device());
+  bf16(gup, "d_up"); bf16(dx, "dx");
+  ok(b200seg_upsample2x_bwd(gup.data_ptr(), nhwc_ld(gup, "d_up"), dx.data_ptr(), nhwc_ld(dx, "dx"),
+                            (int)dx.size(0), (int)dx.size(1), (int)dx.size(2), (int)dx.size(3), cur()),
+     "upsample2x_bwd");
+}
+
+// ---- tensor-core convolutions (csrc/conv) ---------------------------------------------------------
+Tensor conv3x3_fwd(const Tensor& x, const Tensor& w, const OptT& bias, Tensor y, bool want_stats) {
+  c10::cuda::CUDAGuard g(x.device());
+  bf16(x, "x"); bf16(w, "w"); bf16(y, "y");
+  const int N = (int)x.size(0), H = (int)x.size(1), W = (int)x.size(2);
+  const int Cout = (int)w.size(0), Cin = (int)w.size(3);
+  TORCH_CHECK(w.is_contiguous() && w.size(1) == 3 && w.size(2) == 3, "w must be (Cout,3,3,Cin) contiguous");
+  TORCH_CHECK(x.size(3) >= Cin && y.size(3) == Cout, "channel mismatch");
+  int rows = b200conv_fprop_stat_rows(N, H, W, Cin, Cout);
+  Tensor part = want_stats ? at::empty({rows, 2, Cout}, x.options().dtype(at::kFloat)) : Tensor();
+  ok(b200conv_fprop(x.data_ptr(), nhwc_ld(x, "x"), w.data_ptr(), bias.has_value() ? f32(*bias) : nullptr,
+                    y.data_ptr(), nhwc_ld(y, "y"), N, H, W, Cin, Cout, want_stats ? part.data_ptr<float>() : nullptr,
+                    cur()), "conv3x3_fwd");
+  return part;
+}
+
+void conv3x3_dgrad(const Tensor& dy, const Tensor& w, Tensor dx) {
+  c10::cuda::CUDAGuard g(dy.device());
+  bf16(dy, "dy"); bf16(w, "w"); bf16(dx, "dx");
+  const int Cout = (int)w.size(0), Cin = (int)w.size(3);
+  TORCH_CHECK(dx.size(3) == Cin && dy.size(3) == Cout, "channel mismatch");
+  ok(b200conv_dgrad(dy.data_ptr(), nhwc_ld(dy, "dy"), w.data_ptr(), dx.data_ptr(), nhwc_ld(dx, "dx"),
+                    (int)dy.size(0), (int)dy.size(1), (int)dy.size(2), Cin, Cout, cur()), "conv3x3_dgrad");
+}
+
+void conv3x3_wgrad(const Tensor& x, const Tensor& dy, Tensor dw) {
+  c10::cuda::CUDAGuard g(x.device());
+  bf16(x, "x"); bf16(dy, "dy");
+  const int Cout = (int)dw.size(0), Cin = (int)dw.size(3);
+  TORCH_CHECK(dw.is_contiguous() && dw.scalar_type() == at::kFloat, "dw must be fp32 (Cout,3,3,Cin) contiguous");
+  ok(b200conv_wgrad(x.data_ptr(), nhwc_ld(x, "x"), dy.data_ptr(), nhwc_ld(dy, "dy"), dw.data_ptr<float>(),
+                    (int)x.size(0), (int)x.size(1), (int)x.size(2), Cin, Cout, cur()), "conv3x3_wgrad");
+}
+
+void convT2x2_fwd(const Tensor& x, const Tensor& w, const Tensor& bias, Tensor out) {
+  c10::cuda::CUDAGuard g(x.device());
+  bf16(x, "x"); bf16(w, "w"); bf16(out, "out");
+  const int Cin = (int)w.size(1), Cout = (int)w.size(0) / 4;
+  TORCH_CHECK(w.is_contiguous() && x.size(3) == Cin && out.size(3) == Cout, "convT2x2_fwd shapes");
+  ok(b200conv_convT_fwd(x.data_ptr(), nhwc_ld(x, "x"), w.data_ptr(), f32(bias), out.data_ptr(),
+                        nhwc_ld(out, "out"), (int)x.size(0), (int)x.size(1), (int)x.size(2), Cin, Cout, cur()),
+     "convT2x2_fwd");
+}
+
+bool conv_supported(int64_t cin, int64_t cout) { return b200conv_supported((int)cin, (int)cout) != 0; }
+
+}  // namespace
+
+TORCH_LIBRARY(b200seg, m) {
+  m.def("stats_rows() -> int", &stats_rows);
+  m.def("conv_supported(int cin, int cout) -> bool", &conv_supported);
+  m.def("channel_stats(Tensor y, Tensor(a!) partial) -> ()", &channel_stats);
+  m.def("bn_finalize(Tensor? partial, int count, Tensor gamma, Tensor beta, Tensor(a!) running_mean, "
+        "Tensor(b!) running_var, Tensor(c!) num_batches_tracked, Tensor(d!) ss, float momentum, float eps, "
+        "bool training) -> ()", &bn_finalize);
+  m.def("bn_relu_pool_fwd(Tensor y, Tensor ss, Tensor(a!) out, Tensor(b!)? pool) -> ()", &bn_relu_pool_fwd);
+  m.def("bn_relu_pool_bwd(Tensor? d_out, Tensor? d_pool, Tensor y, Tensor ss, Tensor gamma, Tensor(a!) dgamma, "
+        "Tensor(b!) dbeta, Tensor? dbias, Tensor(c!) dy) -> ()", &bn_relu_pool_bwd);
+  m.def("head_ce_fwd_bwd(Tensor a, Tensor w, Tensor b, Tensor labels, float grad_scale, Tensor(a!)? da, "
+        "Tensor(b!)? dw, Tensor(c!)? db, Tensor(d!)? pred, Tensor(e!) loss_acc) -> ()", &head_ce_fwd_bwd);
+  m.def("fused_adam(Tensor(a!) p, Tensor(b!) g, Tensor(c!) m, Tensor(d!) v, float lr, float beta1, float beta2, "
+        "float eps, float weight_decay, float grad_scale, float bc1, float bc2, Tensor(e!)? p_lowp, "
+        "bool zero_grad) -> ()", &fused_adam);
+  m.def("fused_sgd(Tensor(a!) p, Tensor(b!) g, Tensor(c!)? buf, float lr, float momentum, float weight_decay, "
+        "float grad_scale, Tensor(d!)? p_lowp, bool zero_grad, bool first_step) -> ()", &fused_sgd);
+  m.def("amax(Tensor x, Tensor(a!) out) -> ()", &amax);
+  m.def("codec_encode(Tensor x, Tensor scale, Tensor(a!) out_bytes, str codec) -> ()", &codec_encode);
+  m.def("codec_decode(Tensor in_bytes, Tensor scale, Tensor(a!) out, str codec, bool accumulate) -> ()",
+        &codec_decode);
+  m.def("prep_input(Tensor img, Tensor(a!) out) -> ()", &prep_input);
+  m.def("upsample_bilinear2x_fwd(Tensor x, Tensor(a!) out) -> ()", &upsample_fwd);
+  m.def("upsample_bilinear2x_bwd(Tensor d_up, Tensor(a!) dx) -> ()", &upsample_bwd);
+  m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);
+  m.def("conv3x3_dgrad(Tensor dy, Tensor w, Tensor(a!) dx) -> ()", &conv3x3_dgrad);
+  m.def("conv3x3_wgrad(Tensor x, Tensor dy, Tensor(a!) dw) -> ()", &conv3x3_wgrad);
+  m.def("convT2x2_fwd(Tensor x, Tensor w, Tensor bias, Tensor(a!) out) -> ()", &convT2x2_fwd);
+}

@@ -1,0 +1,687 @@
+// Implicit-GEMM convolutions on the 5th-generation tensor cores (tcgen05.mma, TMEM accumulators,
+// TMA-fed shared memory), bf16 NHWC, fp32 accumulation.
+//
+// What this replaces: the reference's nn.Conv2d(k=3, pad=1) forward (R:579, R:582) and its
+// autograd data-gradient, and nn.ConvTranspose2d(k=2, s=2) forward (R:607) -- cuDNN calls made by
+// PyTorch eager.  One kernel template, the "tap GEMM":
+//
+//     D[p][n] = sum_{t < taps} sum_{k < Kc}  A[p + off(t)][k] * B_t[n][k]      (+ bias[n])
+//
+//   fprop   : A = x,  taps = 9, off = (r-1, s-1), B_t[n][k] = W[n][t][k]   (K-major  B operand)
+//   dgrad   : A = dy, taps = 9, off = (1-r, 1-s), B_t[n][k] = W[k][t][n]   (MN-major B operand: the
+//             SAME bf16 weight buffer, read un-transposed -- no transposed copy is ever made)
+//   convT2x2: A = x,  taps = 1, B[n=(q,co)][k] = Wt[q][co][k]; the epilogue scatters column block q
+//             to output pixel (2y+dy, 2x+dx) of the concat buffer's first channels (removes
+//             torch.cat, R:616).
+//
+// Structure (persistent, 1 CTA / SM, 192 threads):
+//   warp 0      TMA producer: per (tap, 64-channel chunk) one 4-D box of the activation (128 pixels
+//               = TN images x TH rows x TW columns; out-of-image coordinates are zero-filled by TMA,
+//               which IS the conv padding) + the weight tile, into a ring of smem stages.
+//   warp 1      allocates TMEM, then a single elected thread issues tcgen05.mma (128 x BLOCK_N x 16)
+//               over the ring; tcgen05.commit releases smem stages and publishes the accumulator.
+//   warps 2-5   epilogue: tcgen05.ld accumulator -> registers, + bias, -> bf16 -> swizzled smem
+//               staging tile -> TMA store (clips at the image edge, honours the channel-slice
+//               stride).  For fprop the BatchNorm batch statistics (sum, sum of squares of the
+//               rounded outputs) are accumulated from the staging tile, so BN costs no extra pass
+//               over the conv output.
+//   TMEM holds two accumulators (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of
+//   tile i+1.
+#include "umma.cuh"
+#include "../common.cuh"
+#include "b200seg.h"
+#include <mutex>
+
+namespace b200 {
+
+constexpr int kConvThreads = 192;
+constexpr int kMaxStages = 8;
+constexpr int kMaxGroups = 8;
+constexpr uint32_t kSmemBudget = 222 * 1024;
+
+struct TapGemmParams {
+  int tiles_w, tiles_h, tiles_g, m_tiles;
+  int tw_log2, th_log2, tn;        // TW = 1 << tw_log2, TH = 1 << th_log2, TN images per tile
+  int H, W, N;
+  int taps, flip;
+  int kc_per_tap;                  // K chunks (of BLOCK_K channels) per tap
+  int kc_total;                    // channels per tap (K-major B: column stride between taps)
+  int n_tiles, block_n, n_total;
+  int b_tap_stride;                // MN-major B: column offset between taps
+  int ocb, groups;                 // output channel box (64/32/16) and groups per N tile
+  int out_mode;                    // 0: NHWC store, 1: convT 2x2 scatter
+  int convt_cout;
+  int stages;
+  uint32_t a_bytes, b_bytes, stage_bytes, staging_bytes;
+  const float* bias;
+  float* partials;
+};
+
+template <int BLOCK_K>
+struct KCfg {
+  static constexpr uint32_t kRowBytes = BLOCK_K * 2;
+  static constexpr uint32_t kLayout = BLOCK_K == 64 ? LAYOUT_SW128 : (BLOCK_K == 32 ? LAYOUT_SW64 : LAYOUT_SW32);
+  static constexpr uint32_t kSBO = 8 * kRowBytes;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int n) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+template <int BLOCK_K, bool B_MN>
+__global__ void __launch_bounds__(kConvThreads, 1)
+tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                const __grid_constant__ CUtensorMap map_o, const TapGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + (size_t)p.stages * p.stage_bytes;
+  __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
+  __shared__ __align__(8) uint64_t bar_tfull[2], bar_tempty[2];
+  __shared__ uint32_t tmem_base_s;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x % p.n_tiles;
+  const int m_first = blockIdx.x / p.n_tiles;
+  const int m_step = gridDim.x / p.n_tiles;
+  const int TW = 1 << p.tw_log2, TH = 1 << p.th_log2;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_o);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(&tmem_base_s);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  const int k_iters = p.taps * p.kc_per_tap;
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int m = m_first; m < p.m_tiles; m += m_step) {
+        const int twi = m % p.tiles_w;
+        const int thi = (m / p.tiles_w) % p.tiles_h;
+        const int g = m / (p.tiles_w * p.tiles_h);
+        const int w0 = twi << p.tw_log2, h0 = thi << p.th_log2, n0 = g * p.tn;
+        for (int t = 0; t < p.taps; ++t) {
+          const int dh = (p.taps == 9) ? p.flip * (t / 3 - 1) : 0;
+          const int dw = (p.taps == 9) ? p.flip * (t % 3 - 1) : 0;
+          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+            MBAR_WAIT_OR_TRAP(&bar_empty[stage], phase ^ 1);
+            uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+            uint8_t* sb = sa + p.a_bytes;
+            mbar_arrive_expect_tx(&bar_full[stage], p.a_bytes + p.b_bytes);
+            tma_load_4d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, w0 + dw, h0 + dh, n0);
+            if (!B_MN) {
+              tma_load_2d(sb, &map_b, &bar_full[stage], t * p.kc_total + kc * BLOCK_K, n_tile * p.block_n);
+            } else {
+              const int nblocks = (p.block_n + 63) >> 6;
+              for (int nb = 0; nb < nblocks; ++nb)
+                tma_load_2d(sb + nb * (BLOCK_K * 128), &map_b, &bar_full[stage],
+                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * BLOCK_K);
+            }
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer ========================================
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(128, p.block_n, 0, B_MN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int m = m_first; m < p.m_tiles; m += m_step) {
+        MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        for (int it = 0; it < k_iters; ++it) {
+          MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
+          const uint32_t sb = sa + p.a_bytes;
+#pragma unroll
+          for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
+            const uint64_t da = make_smem_desc(sa + k4 * 32, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+            uint64_t db;
+            if (!B_MN) db = make_smem_desc(sb + k4 * 32, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+            else       db = make_smem_desc(sb + k4 * 2048, BLOCK_K * 128, 1024, LAYOUT_SW128);
+            umma_bf16(d_tmem, da, db, idesc, (it | k4) != 0 ? 1u : 0u);
+          }
+          umma_commit(&bar_empty[stage]);                 // frees the smem stage when the MMAs retire
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&bar_tfull[acc]);                     // accumulator complete
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================== epilogue ==========================================
+    const int rb = warp & 3;                              // TMEM lane quarter this warp may read
+    const int row = rb * 32 + lane;                       // tile row (pixel) owned by this thread
+    const int et = threadIdx.x - 64;                      // 0..127 within the epilogue group
+    const int ocb = p.ocb;
+    const int ocb_log2 = (ocb == 64) ? 6 : (ocb == 32 ? 5 : 4);
+    const uint32_t row_bytes = ocb * 2;
+    const uint32_t swz_mask = (row_bytes >> 4) - 1;       // 16-byte chunks per row - 1
+    const uint32_t group_bytes = 128 * row_bytes;
+    float st_s[kMaxGroups], st_q[kMaxGroups];
+#pragma unroll
+    for (int g = 0; g < kMaxGroups; ++g) st_s[g] = st_q[g] = 0.f;
+    const int st_c = et & (ocb - 1);                      // channel (within a group) for statistics
+    const int st_r0 = (et >> ocb_log2) * ocb;             // first of the `ocb` rows this thread sums
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int m = m_first; m < p.m_tiles; m += m_step) {
+      const int twi = m % p.tiles_w;
+      const int thi = (m / p.tiles_w) % p.tiles_h;
+      const int g_img = m / (p.tiles_w * p.tiles_h);
+      const int w0 = twi << p.tw_log2, h0 = thi << p.th_log2, n0 = g_img * p.tn;
+      MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + acc * 256 + (static_cast<uint32_t>(rb * 32) << 16);
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t r[32];
+        if (p.block_n - c0 >= 32) {
+          tmem_ld_32x32b_x32(t_addr + c0, r);
+        } else {
+          uint32_t r16[16];
+          tmem_ld_32x32b_x16(t_addr + c0, r16);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
+        }
+        tmem_ld_wait();
+        const int ncols = (p.block_n - c0 >= 32) ? 32 : 16;
+        const int col0 = n_tile * p.block_n + c0;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {                     // four 16-byte chunks of 8 channels
+          if (v * 8 < ncols) {
+            float f[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float b = 0.f;
+              if (p.bias != nullptr) {
+                const int col = col0 + v * 8 + j;
+                b = __ldg(p.bias + (p.out_mode == 1 ? (col % p.convt_cout) : col));
+              }
+              f[j] = __uint_as_float(r[v * 8 + j]) + b;
+            }
+            const int cg = c0 + v * 8;                    // column within the N tile
+            const int grp = cg >> ocb_log2;
+            const uint32_t chunk = (cg & (ocb - 1)) >> 3;
+            const uint32_t off = row * row_bytes + (chunk << 4);
+            const uint32_t phys = off ^ (((off >> 7) & swz_mask) << 4);
+            *reinterpret_cast<bf16x8*>(staging + grp * group_bytes + phys) = pack8(f);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&bar_tempty[acc]);                      // accumulator drained: MMA may reuse it
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      fence_proxy_async();                                // staging writes -> visible to TMA
+      named_bar_sync(1, 128);
+      if (p.partials != nullptr) {
+        const bool full_tile = (w0 + TW <= p.W) && (h0 + TH <= p.H) && (n0 + p.tn <= p.N);
+        for (int g = 0; g < p.groups; ++g) {
+          float s = 0.f, q = 0.f;
+          const uint8_t* gb = staging + g * group_bytes;
+          for (int i = 0; i < ocb; ++i) {
+            const int rr = st_r0 + i;
+            bool valid = true;
+            if (!full_tile) {
+              const int tw_ = rr & (TW - 1), th_ = (rr >> p.tw_log2) & (TH - 1), tn_ = rr >> (p.tw_log2 + p.th_log2);
+              valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
+            }
+            const uint32_t off = rr * row_bytes + ((st_c >> 3) << 4);
+            const uint32_t phys = (off ^ (((off >> 7) & swz_mask) << 4)) + (st_c & 7) * 2;
+            const float v = valid ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + phys)) : 0.f;
+            s += v;
+            q = fmaf(v, v, q);
+          }
+#pragma unroll
+          for (int gg = 0; gg < kMaxGroups; ++gg)
+            if (gg == g) { st_s[gg] += s; st_q[gg] += q; }
+        }
+      }
+      if (et == 0) {
+        for (int g = 0; g < p.groups; ++g) {
+          const int ch0 = n_tile * p.block_n + g * ocb;
+          if (p.out_mode == 0) {
+            tma_store_4d(&map_o, staging + g * group_bytes, ch0, w0, h0, n0);
+          } else {
+            const int q = ch0 / p.convt_cout, co0 = ch0 % p.convt_cout;
+            tma_store_5d(&map_o, staging + g * group_bytes, co0, q & 1, w0, q >> 1, n0 * p.H + h0);
+          }
+        }
+        tma_store_commit();
+        tma_store_wait_read<0>();                          // staging may be overwritten again
+      }
+      named_bar_sync(1, 128);
+    }
+    if (p.partials != nullptr) {
+      // combine the (128 / ocb) threads that share a channel, then one row of partials per CTA
+      float* red = reinterpret_cast<float*>(staging);    // [128/ocb][2][groups*ocb]
+      const int tpc = 128 >> ocb_log2;
+      const int ncol = p.groups * ocb;
+      for (int g = 0; g < p.groups; ++g) {
+        float s = 0.f, q = 0.f;
+#pragma unroll
+        for (int gg = 0; gg < kMaxGroups; ++gg)
+          if (gg == g) { s = st_s[gg]; q = st_q[gg]; }
+        red[((et >> ocb_log2) * 2 + 0) * ncol + g * ocb + st_c] = s;
+        red[((et >> ocb_log2) * 2 + 1) * ncol + g * ocb + st_c] = q;
+      }
+      named_bar_sync(1, 128);
+      for (int c = et; c < ncol; c += 128) {
+        float s = 0.f, q = 0.f;
+        for (int i = 0; i < tpc; ++i) { s += red[(i * 2 + 0) * ncol + c]; q += red[(i * 2 + 1) * ncol + c]; }
+        const int col = n_tile * p.block_n + c;
+        if (col < p.n_total) {
+          p.partials[((size_t)m_first * 2 + 0) * p.n_total + col] = s;
+          p.partials[((size_t)m_first * 2 + 1) * p.n_total + col] = q;
+        }
+      }
+    }
+    if (et == 0) tma_store_wait_all<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// =================================================================================================
+// Weight gradient:  dW[co][t][ci] += sum_p dy[p][co] * x[p + off(t)][ci]     
+// GEMM view: D[(t, ci)][co], M = 9*Cin walked in 64-channel blocks (an M tile of 128 rows pairs two
+// blocks, possibly of different taps), N = Cout, K = pixels (64 per stage).  Both operands are
+// "MN-major" (the reduction index, the pixel, is the slow one in NHWC memory), which tcgen05 reads
+// directly -- no transposes.  K is split across CTAs; partial tiles are added into the fp32
+// gradient buffer with red.global.add (the buffer accumulates across micro-batches anyway, R:756).
+struct WgradParams {
+  int tiles_w, tiles_h, tiles_g, p_tiles;   // pixel tiles of 64
+  int tw_log2, th_log2, tn;
+  int Cin, Cout;
+  int chunks_per_tap;                       // ceil(Cin / 64)
+  int m_blocks, m_tiles;                    // 64-row blocks (9 * chunks_per_tap) and 128-row tiles
+  int n_tiles, block_n;
+  int k_slices;
+  int stages;
+  uint32_t a_bytes, b_bytes, stage_bytes;
+  float* dw;
+};
+
+__global__ void __launch_bounds__(kConvThreads, 1)
+wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
+             const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
+  __shared__ __align__(8) uint64_t bar_tfull;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  int id = blockIdx.x;
+  const int n_tile = id % p.n_tiles; id /= p.n_tiles;
+  const int m_tile = id % p.m_tiles; id /= p.m_tiles;
+  const int ks = id;
+  const int per = (p.p_tiles + p.k_slices - 1) / p.k_slices;
+  const int pt0 = ks * per;
+  const int pt1 = min(p.p_tiles, pt0 + per);
+  const int k_iters = pt1 - pt0;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_dy);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    mbar_init(&bar_tfull, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<256>(&tmem_base_s);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  const int nblocks = (p.block_n + 63) >> 6;
+
+  if (k_iters > 0) {
+    if (warp == 0) {
+      if (elect_one()) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int pt = pt0; pt < pt1; ++pt) {
+          const int twi = pt % p.tiles_w;
+          const int thi = (pt / p.tiles_w) % p.tiles_h;
+          const int g = pt / (p.tiles_w * p.tiles_h);
+          const int w0 = twi << p.tw_log2, h0 = thi << p.th_log2, n0 = g * p.tn;
+          MBAR_WAIT_OR_TRAP(&bar_empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+          uint8_t* sb = sa + p.a_bytes;
+          mbar_arrive_expect_tx(&bar_full[stage], p.a_bytes + p.b_bytes);
+          for (int hb = 0; hb < 2; ++hb) {
+            int blk = m_tile * 2 + hb;
+            if (blk >= p.m_blocks) blk = p.m_blocks - 1;     // padding block: loaded, never stored
+            const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
+            tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + (t % 3 - 1), h0 + (t / 3 - 1), n0);
+          }
+          for (int nb = 0; nb < nblocks; ++nb)
+            tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        const uint32_t idesc = make_idesc_bf16(128, p.block_n, 1, 1);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int it = 0; it < k_iters; ++it) {
+          MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
+          const uint32_t sb = sa + p.a_bytes;
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4) {
+            const uint64_t da = make_smem_desc(sa + k4 * 2048, 8192, 1024, LAYOUT_SW128);
+            const uint64_t db = make_smem_desc(sb + k4 * 2048, 8192, 1024, LAYOUT_SW128);
+            umma_bf16(tmem_base, da, db, idesc, (it | k4) != 0 ? 1u : 0u);
+          }
+          umma_commit(&bar_empty[stage]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&bar_tfull);
+      }
+    } else {
+      const int rb = warp & 3;
+      const int row = rb * 32 + lane;
+      int blk = m_tile * 2 + (row >> 6);
+      const bool blk_ok = blk < p.m_blocks;
+      if (!blk_ok) blk = p.m_blocks - 1;
+      const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
+      const int ci = cc * 64 + (row & 63);
+      const bool row_ok = blk_ok && ci < p.Cin;
+      MBAR_WAIT_OR_TRAP(&bar_tfull, 0);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(rb * 32) << 16);
+      float* base = p.dw + (size_t)t * p.Cin + ci;
+      const size_t co_stride = (size_t)9 * p.Cin;
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t r[32];
+        if (p.block_n - c0 >= 32) {
+          tmem_ld_32x32b_x32(t_addr + c0, r);
+        } else {
+          uint32_t r16[16];
+          tmem_ld_32x32b_x16(t_addr + c0, r16);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
+        }
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int co = n_tile * p.block_n + c0 + j;
+            if (c0 + j < p.block_n && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(r[j]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+// =================================================================================================
+// Host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+static CUtensorMapSwizzle swizzle_for_bytes(int inner_bytes) {
+  if (inner_bytes >= 128) return CU_TENSOR_MAP_SWIZZLE_128B;
+  if (inner_bytes >= 64) return CU_TENSOR_MAP_SWIZZLE_64B;
+  return CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
+// rank-R bf16 tensor map; dims[0] is the contiguous one; strides in elements for dims 1..R-1.
+static bool make_map(CUtensorMap* m, const void* base, int rank, const long long* dims, const long long* strides_el,
+                     const int* box, int inner_bytes) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = (cuuint64_t)dims[i]; b[i] = (cuuint32_t)box[i]; e[i] = 1; }
+  for (int i = 1; i < rank; ++i) s[i - 1] = (cuuint64_t)strides_el[i] * 2;
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, e,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for_bytes(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+static int ilog2_floor(int x) { int l = 0; while ((2 << l) <= x) ++l; return l; }
+
+struct TileGeom { int tw_log2, th_log2, tn, tiles_w, tiles_h, tiles_g; };
+
+static TileGeom geom_for(int N, int H, int W, int pixels) {
+  TileGeom g;
+  const int pl = ilog2_floor(pixels);
+  g.tw_log2 = ilog2_floor(W < 16 ? W : 16);
+  int rem = pl - g.tw_log2;
+  g.th_log2 = ilog2_floor(H);
+  if (g.th_log2 > rem) g.th_log2 = rem;
+  g.tn = 1 << (pl - g.tw_log2 - g.th_log2);
+  g.tiles_w = (W + (1 << g.tw_log2) - 1) >> g.tw_log2;
+  g.tiles_h = (H + (1 << g.th_log2) - 1) >> g.th_log2;
+  g.tiles_g = (N + g.tn - 1) / g.tn;
+  return g;
+}
+
+static int pick_block_k(int kc) { return kc % 64 == 0 ? 64 : (kc % 32 == 0 ? 32 : (kc % 16 == 0 ? 16 : 0)); }
+static int pick_ocb(int n) { return n % 64 == 0 ? 64 : (n % 32 == 0 ? 32 : 16); }
+static int pick_block_n(int n_total, int ocb) {
+  if (n_total <= 256) return n_total;
+  if (ocb == 64) {
+    if (n_total % 256 == 0) return 256;
+    if (n_total % 128 == 0) return 128;
+    return 64;
+  }
+  return ocb * (256 / ocb >= kMaxGroups ? kMaxGroups : 256 / ocb);
+}
+
+template <int BK, bool BMN>
+static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const TapGemmParams& p,
+                      int grid, size_t smem, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(tap_gemm_kernel<BK, BMN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(kSmemBudget + 2048));
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  tap_gemm_kernel<BK, BMN><<<grid, kConvThreads, smem, st>>>(ma, mb, mo, p);
+  return (int)cudaGetLastError();
+}
+
+// mode: 0 fprop, 1 dgrad, 2 convT forward
+static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, const float* bias, void* out,
+                        long long ld_o, int N, int H, int W, int Kc, int n_total, int conv_cin, float* partials,
+                        int* stat_rows_out, bool dry, cudaStream_t st) {
+  const int BK = pick_block_k(Kc);
+  if (BK == 0 || n_total % 16) return (int)cudaErrorInvalidValue;
+  TapGemmParams p{};
+  TileGeom g = geom_for(N, H, W, 128);
+  p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
+  p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
+  p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
+  p.H = H; p.W = W; p.N = N;
+  p.taps = (mode == 2) ? 1 : 9;
+  p.flip = (mode == 1) ? -1 : 1;
+  p.kc_per_tap = Kc / BK;
+  p.kc_total = Kc;
+  p.n_total = n_total;
+  p.ocb = pick_ocb(mode == 2 ? n_total / 4 : n_total);
+  p.block_n = pick_block_n(n_total, p.ocb);
+  if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
+  p.n_tiles = (n_total + p.block_n - 1) / p.block_n;
+  p.groups = p.block_n / p.ocb;
+  if (p.groups > kMaxGroups || p.block_n % p.ocb) return (int)cudaErrorInvalidValue;
+  p.b_tap_stride = conv_cin;
+  p.out_mode = (mode == 2) ? 1 : 0;
+  p.convt_cout = (mode == 2) ? n_total / 4 : 1;
+  if (mode == 2 && (p.convt_cout % p.ocb)) return (int)cudaErrorInvalidValue;
+  if (mode == 2 && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
+  p.bias = bias;
+  p.partials = partials;
+  p.a_bytes = 128 * BK * 2;
+  const bool bmn = (mode == 1);
+  const uint32_t b_raw = bmn ? (uint32_t)((p.block_n + 63) / 64) * 64 * BK * 2 : (uint32_t)p.block_n * BK * 2;
+  p.b_bytes = b_raw;
+  p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
+  p.staging_bytes = 128u * p.block_n * 2;
+  if (p.staging_bytes < 4096) p.staging_bytes = 4096;
+  int stages = (int)((kSmemBudget - p.staging_bytes) / p.stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return (int)cudaErrorInvalidValue;
+  p.stages = stages;
+  int grid = kNumSMs - (kNumSMs % p.n_tiles);
+  const long long total = (long long)p.m_tiles * p.n_tiles;
+  if (total < grid) grid = (int)total;
+  if (stat_rows_out) *stat_rows_out = grid / p.n_tiles;
+  if (dry) return 0;
+
+  CUtensorMap ma, mb, mo;
+  const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
+  {
+    long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
+    int box[4] = {BK, TW, TH, g.tn};
+    if (!make_map(&ma, a, 4, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
+  }
+  if (!bmn) {      // weights as [n_total rows][taps*Kc cols], K contiguous
+    long long dims[2] = {(long long)p.taps * Kc, n_total}, str[2] = {1, (long long)p.taps * Kc};
+    int box[2] = {BK, p.block_n};
+    if (!make_map(&mb, w, 2, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
+  } else {         // weights as [Kc rows (conv Cout)][9*conv_cin cols], N contiguous
+    long long dims[2] = {(long long)9 * conv_cin, Kc}, str[2] = {1, (long long)9 * conv_cin};
+    int box[2] = {64, BK};
+    if (!make_map(&mb, w, 2, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  }
+  if (mode != 2) {
+    long long dims[4] = {n_total, W, H, N}, str[4] = {1, ld_o, ld_o * W, ld_o * W * H};
+    int box[4] = {p.ocb, TW, TH, g.tn};
+    if (!make_map(&mo, out, 4, dims, str, box, p.ocb * 2)) return (int)cudaErrorInvalidValue;
+  } else {         // (c, dx, x, dy, Y = n*h + y) view of the (N, 2h, 2w, C) output
+    long long dims[5] = {p.convt_cout, 2, W, 2, (long long)N * H};
+    long long str[5] = {1, ld_o, 2 * ld_o, 2 * (long long)W * ld_o, 4 * (long long)W * ld_o};
+    int box[5] = {p.ocb, 1, TW, 1, TH * g.tn};
+    if (!make_map(&mo, out, 5, dims, str, box, p.ocb * 2)) return (int)cudaErrorInvalidValue;
+  }
+  const size_t smem = (size_t)p.stages * p.stage_bytes + p.staging_bytes + 1024;
+  if (bmn) {
+    if (BK == 64) return launch_tap<64, true>(ma, mb, mo, p, grid, smem, st);
+    if (BK == 32) return launch_tap<32, true>(ma, mb, mo, p, grid, smem, st);
+    return launch_tap<16, true>(ma, mb, mo, p, grid, smem, st);
+  }
+  if (BK == 64) return launch_tap<64, false>(ma, mb, mo, p, grid, smem, st);
+  if (BK == 32) return launch_tap<32, false>(ma, mb, mo, p, grid, smem, st);
+  return launch_tap<16, false>(ma, mb, mo, p, grid, smem, st);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200conv_supported(int cin, int cout) { return (cin % 16 == 0 && cout % 16 == 0) ? 1 : 0; }
+
+extern "C" int b200conv_fprop_stat_rows(int N, int H, int W, int Cin, int Cout) {
+  int rows = 0;
+  int e = run_tap_gemm(0, nullptr, Cin, nullptr, nullptr, nullptr, Cout, N, H, W, Cin, Cout, Cin, nullptr, &rows,
+                       true, 0);
+  return e == 0 ? rows : 0;
+}
+
+extern "C" int b200conv_fprop(const void* x, long long ld_x, const void* w, const float* bias, void* y,
+                              long long ld_y, int N, int H, int W, int Cin, int Cout, float* partials,
+                              cudaStream_t st) {
+  return run_tap_gemm(0, x, ld_x, w, bias, y, ld_y, N, H, W, Cin, Cout, Cin, partials, nullptr, false, st);
+}
+
+extern "C" int b200conv_dgrad(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
+                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+  return run_tap_gemm(1, dy, ld_dy, w, nullptr, dx, ld_dx, N, H, W, Cout, Cin, Cin, nullptr, nullptr, false, st);
+}
+
+extern "C" int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, const float* bias, void* out,
+                                  long long ld_o, int N, int h, int w_, int Cin, int Cout, cudaStream_t st) {
+  return run_tap_gemm(2, x, ld_x, w, bias, out, ld_o, N, h, w_, Cin, 4 * Cout, Cin, nullptr, nullptr, false, st);
+}
+
+extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+  if (Cin % 8 || Cout % 16) return (int)cudaErrorInvalidValue;
+  WgradParams p{};
+  TileGeom g = geom_for(N, H, W, 64);
+  p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
+  p.p_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
+  p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
+  p.Cin = Cin; p.Cout = Cout;
+  p.chunks_per_tap = (Cin + 63) / 64;
+  p.m_blocks = 9 * p.chunks_per_tap;
+  p.m_tiles = (p.m_blocks + 1) / 2;
+  p.block_n = Cout <= 256 ? Cout : (Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64));
+  if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
+  p.n_tiles = (Cout + p.block_n - 1) / p.block_n;
+  const int nblocks = (p.block_n + 63) / 64;
+  p.a_bytes = 2 * 8192;
+  p.b_bytes = nblocks * 8192;
+  p.stage_bytes = p.a_bytes + p.b_bytes;
+  int stages = (int)(kSmemBudget / p.stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  p.stages = stages;
+  const int base_items = p.m_tiles * p.n_tiles;
+  int ks = (2 * kNumSMs) / base_items;
+  if (ks < 1) ks = 1;
+  if (ks > p.p_tiles) ks = p.p_tiles;
+  p.k_slices = ks;
+  p.dw = dw;
+  CUtensorMap mx, mdy;
+  const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
+  {
+    long long dims[4] = {Cin, W, H, N}, str[4] = {1, ld_x, ld_x * W, ld_x * W * H};
+    int box[4] = {64, TW, TH, g.tn};
+    if (!make_map(&mx, x, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  }
+  {
+    long long dims[4] = {Cout, W, H, N}, str[4] = {1, ld_dy, ld_dy * W, ld_dy * W * H};
+    int box[4] = {64, TW, TH, g.tn};
+    if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  }
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(kSmemBudget + 2048));
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  const size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
+  wgrad_kernel<<<base_items * ks, kConvThreads, smem, st>>>(mx, mdy, p);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,401 @@
+// BatchNorm(train) + ReLU (+ 2x2 max-pool) forward and backward on NHWC bf16 tensors.
+//
+// Replaces, per conv stage of the reference's DoubleConv (R:578-585) and DownBlock (R:595):
+// cuDNN/ATen batch_norm (stats pass + normalise pass), the in-place ReLU, max_pool2d and their
+// backward kernels.  The per-channel statistics of the forward come out of the
+// conv epilogue (csrc/conv) as per-CTA partial sums, so the forward here is ONE pass:
+//   y (raw conv output) -> relu(y*scale+shift) -> skip tensor (a channel slice of the decoder's
+//   concat buffer, which removes torch.cat, R:616) and, for encoder blocks, the pooled tensor.
+// Backward is reduce -> finalize -> apply; the pool's arg-max is recomputed from y (first
+// maximum in row-major window order, as ATen), so no index tensor is stored.
+#include "../common.cuh"
+#include "b200seg.h"
+
+namespace b200 {
+
+constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------------------------------------
+// Per-channel sum / sum of squares of a bf16 NHWC tensor -> partial[gridDim.x][2][C].
+// (Only needed when the conv did not produce the partials itself, i.e. the cuDNN comparison arm.)
+__global__ void __launch_bounds__(kThreads)
+channel_stats_kernel(const __nv_bfloat16* __restrict__ y, long long P, int C, long long ld,
+                     float* __restrict__ partial) {
+  extern __shared__ float sm[];
+  const int CV = C >> 3;
+  const int rows_pb = kThreads / CV;
+  const int cv = threadIdx.x % CV, r = threadIdx.x / CV;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (r < rows_pb) {
+    for (long long p = (long long)blockIdx.x * rows_pb + r; p < P; p += (long long)gridDim.x * rows_pb) {
+      float f[8];
+      unpack8(ld8(y + p * ld + cv * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+    }
+  }
+  float* s_sum = sm;
+  float* s_sq = sm + rows_pb * C;
+  if (r < rows_pb) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_sum[r * C + cv * 8 + j] = s[j]; s_sq[r * C + cv * 8 + j] = q[j]; }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += kThreads) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < rows_pb; ++i) { a += s_sum[i * C + c]; b += s_sq[i * C + c]; }
+    partial[((size_t)blockIdx.x * 2 + 0) * C + c] = a;
+    partial[((size_t)blockIdx.x * 2 + 1) * C + c] = b;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// partial[R][2][C] -> ss[4][C] = scale, shift, mean, invstd; running stats (momentum, unbiased
+// variance) and num_batches_tracked as nn.BatchNorm2d (R:580).
+__global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, long long count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var,
+                                   long long* __restrict__ nbt, float* __restrict__ ss, int C,
+                                   float momentum, float eps, int training) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double mean, var;
+  if (training) {
+    double s = 0.0, q = 0.0;
+    for (int r = 0; r < rows; ++r) {
+      s += (double)partial[((size_t)r * 2 + 0) * C + c];
+      q += (double)partial[((size_t)r * 2 + 1) * C + c];
+    }
+    mean = s / (double)count;
+    var = q / (double)count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    if (running_mean != nullptr) {
+      double unb = var * ((double)count / (double)(count > 1 ? count - 1 : 1));
+      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+      running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unb);
+    }
+    if (c == 0 && nbt != nullptr) *nbt += 1;
+  } else {
+    mean = (double)running_mean[c];
+    var = (double)running_var[c];
+  }
+  const double invstd = rsqrt(var + (double)eps);
+  const double scale = (double)gamma[c] * invstd;
+  ss[0 * C + c] = (float)scale;
+  ss[1 * C + c] = (float)((double)beta[c] - mean * scale);
+  ss[2 * C + c] = (float)mean;
+  ss[3 * C + c] = (float)invstd;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <bool POOL>
+__global__ void __launch_bounds__(kThreads)
+bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ y, long long ld_y,
+                        const float* __restrict__ ss, __nv_bfloat16* __restrict__ out, long long ld_o,
+                        __nv_bfloat16* __restrict__ pool, long long ld_p, int N, int H, int W, int C) {
+  const int CV = C >> 3;
+  const long long P = (long long)N * H * W;
+  const long long items = (POOL ? P / 4 : P) * CV;
+  const int Wo = W >> 1, Ho = H >> 1;
+  int last_cv = -1;
+  float sc[8], sh[8];
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < items;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(idx % CV);
+    const long long pix = idx / CV;
+    if (cv != last_cv) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j); }
+      last_cv = cv;
+    }
+    if (!POOL) {
+      float f[8];
+      unpack8(ld8(y + pix * ld_y + cv * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+      st8(out + pix * ld_o + cv * 8, pack8(f));
+    } else {
+      const int wo = (int)(pix % Wo);
+      const long long t = pix / Wo;
+      const int ho = (int)(t % Ho);
+      const long long n = t / Ho;
+      const long long p00 = (n * H + 2 * ho) * W + 2 * wo;
+      bf16x8 in[4];
+      in[0] = ld8(y + p00 * ld_y + cv * 8);
+      in[1] = ld8(y + (p00 + 1) * ld_y + cv * 8);
+      in[2] = ld8(y + (p00 + W) * ld_y + cv * 8);
+      in[3] = ld8(y + (p00 + W + 1) * ld_y + cv * 8);
+      float m[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) m[j] = 0.f;          // relu output >= 0
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float f[8];
+        unpack8(in[k], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+        bf16x8 o = pack8(f);
+        const long long pp = p00 + (k & 1) + (k >> 1) * W;
+        st8(out + pp * ld_o + cv * 8, o);
+        unpack8(o, f);                                    // pool the rounded values, as torch does
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+      }
+      st8(pool + pix * ld_p + cv * 8, pack8(m));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward pass 1: g = (d_out + route(d_pool)) * [y*scale+shift > 0]; per-channel partial sums of
+// g and g*xhat.  One thread owns one 8-channel group and walks pixels (or 2x2 windows).
+template <bool POOL>
+__device__ __forceinline__ void load_g(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
+                                       const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
+                                       const __nv_bfloat16* __restrict__ y, long long ld_y,
+                                       const float (&sc)[8], const float (&sh)[8], long long pix,
+                                       long long p00, int W, int cv, float (&yv)[4][8],
+                                       float (&g)[4][8]) {
+  constexpr int NP = POOL ? 4 : 1;
+  float a[NP][8];
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const long long pp = POOL ? (p00 + (k & 1) + (k >> 1) * W) : pix;
+    unpack8(ld8(y + pp * ld_y + cv * 8), yv[k]);
+    if (d_out != nullptr) {
+      unpack8(ld8(d_out + pp * ld_do + cv * 8), g[k]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[k][j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[k][j] = fmaf(yv[k][j], sc[j], sh[j]);
+  }
+  if (POOL && d_pool != nullptr) {
+    float dp[8];
+    unpack8(ld8(d_pool + pix * ld_dp + cv * 8), dp);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // the forward pooled bf16-rounded relu outputs; find the first maximum among them
+      float best = -1.f;
+      int arg = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float v = __bfloat162float(__float2bfloat16(fmaxf(a[k][j], 0.f)));
+        if (v > best) { best = v; arg = k; }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) g[k][j] += (k == arg) ? dp[j] : 0.f;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NP; ++k)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[k][j] = (a[k][j] > 0.f) ? g[k][j] : 0.f;
+}
+
+template <bool POOL>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
+                     const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
+                     const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
+                     int N, int H, int W, int C, float* __restrict__ partial) {
+  extern __shared__ float sm[];
+  const int CV = C >> 3;
+  const int rows_pb = kThreads / CV;
+  const int cv = threadIdx.x % CV, r = threadIdx.x / CV;
+  const long long P = (long long)N * H * W;
+  const long long items = POOL ? P / 4 : P;
+  const int Wo = W >> 1, Ho = H >> 1;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (r < rows_pb) {
+    float sc[8], sh[8], mean[8], inv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = ss[cv * 8 + j]; sh[j] = ss[C + cv * 8 + j];
+      mean[j] = ss[2 * C + cv * 8 + j]; inv[j] = ss[3 * C + cv * 8 + j];
+    }
+    for (long long pix = (long long)blockIdx.x * rows_pb + r; pix < items;
+         pix += (long long)gridDim.x * rows_pb) {
+      long long p00 = 0;
+      if (POOL) {
+        const int wo = (int)(pix % Wo);
+        const long long t = pix / Wo;
+        const int ho = (int)(t % Ho);
+        p00 = ((t / Ho) * H + 2 * ho) * W + 2 * wo;
+      }
+      float yv[4][8], g[4][8];
+      load_g<POOL>(d_out, ld_do, d_pool, ld_dp, y, ld_y, sc, sh, pix, p00, W, cv, yv, g);
+#pragma unroll
+      for (int k = 0; k < (POOL ? 4 : 1); ++k)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          s[j] += g[k][j];
+          q[j] = fmaf(g[k][j], (yv[k][j] - mean[j]) * inv[j], q[j]);
+        }
+    }
+  }
+  float* s_sum = sm;
+  float* s_sq = sm + rows_pb * C;
+  if (r < rows_pb) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_sum[r * C + cv * 8 + j] = s[j]; s_sq[r * C + cv * 8 + j] = q[j]; }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += kThreads) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < rows_pb; ++i) { a += s_sum[i * C + c]; b += s_sq[i * C + c]; }
+    partial[((size_t)blockIdx.x * 2 + 0) * C + c] = a;
+    partial[((size_t)blockIdx.x * 2 + 1) * C + c] = b;
+  }
+}
+
+// Backward pass 2 (tiny): finish the two sums, accumulate dgamma / dbeta, and fold everything the
+// apply pass needs into 3 per-channel coefficients: dy = k1*g + e1*y + e0.
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int rows, long long count,
+                                       const float* __restrict__ gamma, const float* __restrict__ ss,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       float* __restrict__ coef, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double sg = 0.0, sgx = 0.0;
+  for (int r = 0; r < rows; ++r) {
+    sg += (double)partial[((size_t)r * 2 + 0) * C + c];
+    sgx += (double)partial[((size_t)r * 2 + 1) * C + c];
+  }
+  dbeta[c] += (float)sg;
+  dgamma[c] += (float)sgx;
+  const double mean = ss[2 * C + c], inv = ss[3 * C + c];
+  const double k1 = (double)gamma[c] * inv;
+  const double c1 = sg / (double)count, c2 = sgx / (double)count;
+  coef[0 * C + c] = (float)k1;
+  coef[1 * C + c] = (float)(-k1 * c2 * inv);
+  coef[2 * C + c] = (float)(k1 * (c2 * mean * inv - c1));
+}
+
+template <bool POOL>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
+                    const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
+                    const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
+                    const float* __restrict__ coef, int N, int H, int W, int C,
+                    __nv_bfloat16* __restrict__ dy, long long ld_dy) {
+  const int CV = C >> 3;
+  const long long P = (long long)N * H * W;
+  const long long items = (POOL ? P / 4 : P) * CV;
+  const int Wo = W >> 1, Ho = H >> 1;
+  int last_cv = -1;
+  float sc[8], sh[8], k1[8], e1[8], e0[8];
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < items;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(idx % CV);
+    const long long pix = idx / CV;
+    if (cv != last_cv) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j);
+        k1[j] = __ldg(coef + cv * 8 + j); e1[j] = __ldg(coef + C + cv * 8 + j);
+        e0[j] = __ldg(coef + 2 * C + cv * 8 + j);
+      }
+      last_cv = cv;
+    }
+    long long p00 = 0;
+    if (POOL) {
+      const int wo = (int)(pix % Wo);
+      const long long t = pix / Wo;
+      const int ho = (int)(t % Ho);
+      p00 = ((t / Ho) * H + 2 * ho) * W + 2 * wo;
+    }
+    float yv[4][8], g[4][8];
+    load_g<POOL>(d_out, ld_do, d_pool, ld_dp, y, ld_y, sc, sh, pix, p00, W, cv, yv, g);
+#pragma unroll
+    for (int k = 0; k < (POOL ? 4 : 1); ++k) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaf(k1[j], g[k][j], fmaf(e1[j], yv[k][j], e0[j]));
+      const long long pp = POOL ? (p00 + (k & 1) + (k >> 1) * W) : pix;
+      st8(dy + pp * ld_dy + cv * 8, pack8(o));
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200seg_stats_rows() { return 2 * kNumSMs; }
+
+extern "C" int b200seg_channel_stats(const void* y, long long P, int C, long long ld, float* partial,
+                                     int rows, cudaStream_t st) {
+  if (C % 8 || C > 2048) return (int)cudaErrorInvalidValue;
+  const int CV = C / 8, rows_pb = kThreads / CV;
+  if (rows_pb < 1) return (int)cudaErrorInvalidValue;
+  size_t smem = (size_t)2 * rows_pb * C * sizeof(float);
+  channel_stats_kernel<<<rows, kThreads, smem, st>>>((const __nv_bfloat16*)y, P, C, ld, partial);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200seg_bn_finalize(const float* partial, int rows, long long count, const float* gamma,
+                                   const float* beta, float* running_mean, float* running_var,
+                                   long long* nbt, float* ss, int C, float momentum, float eps,
+                                   int training, cudaStream_t st) {
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, count, gamma, beta, running_mean,
+                                                      running_var, nbt, ss, C, momentum, eps, training);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200seg_bn_relu_pool_fwd(const void* y, long long ld_y, const float* ss, void* out,
+                                        long long ld_o, void* pool, long long ld_p, int N, int H, int W,
+                                        int C, cudaStream_t st) {
+  if (C % 8) return (int)cudaErrorInvalidValue;
+  const long long P = (long long)N * H * W;
+  if (pool != nullptr) {
+    if ((H | W) & 1) return (int)cudaErrorInvalidValue;
+    int grid = grid_for(P / 4 * (C / 8), kThreads);
+    bn_relu_pool_fwd_kernel<true><<<grid, kThreads, 0, st>>>(
+        (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, (__nv_bfloat16*)pool, ld_p, N, H, W, C);
+  } else {
+    int grid = grid_for(P * (C / 8), kThreads);
+    bn_relu_pool_fwd_kernel<false><<<grid, kThreads, 0, st>>>(
+        (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, nullptr, 0, N, H, W, C);
+  }
+  return (int)cudaGetLastError();
+}
+
+// workspace: float[rows*2*C + 3*C]; rows = b200seg_stats_rows().
+extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, const void* d_pool,
+                                        long long ld_dp, const void* y, long long ld_y, const float* ss,
+                                        const float* gamma, float* dgamma, float* dbeta, void* dy,
+                                        long long ld_dy, int N, int H, int W, int C, int pooled,
+                                        float* workspace, cudaStream_t st) {
+  if (C % 8 || C > 2048) return (int)cudaErrorInvalidValue;
+  const int CV = C / 8, rows_pb = kThreads / CV;
+  if (rows_pb < 1) return (int)cudaErrorInvalidValue;
+  const int rows = b200seg_stats_rows();
+  const long long P = (long long)N * H * W;
+  float* partial = workspace;
+  float* coef = workspace + (size_t)rows * 2 * C;
+  size_t smem = (size_t)2 * rows_pb * C * sizeof(float);
+  const __nv_bfloat16 *a = (const __nv_bfloat16*)d_out, *b = (const __nv_bfloat16*)d_pool,
+                      *yy = (const __nv_bfloat16*)y;
+  if (pooled) {
+    bn_bwd_reduce_kernel<true><<<rows, kThreads, smem, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, N, H, W, C, partial);
+  } else {
+    bn_bwd_reduce_kernel<false><<<rows, kThreads, smem, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, N, H, W, C, partial);
+  }
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
+  if (pooled) {
+    int grid = grid_for(P / 4 * CV, kThreads);
+    bn_bwd_apply_kernel<true><<<grid, kThreads, 0, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, coef, N, H, W, C,
+                                                         (__nv_bfloat16*)dy, ld_dy);
+  } else {
+    int grid = grid_for(P * CV, kThreads);
+    bn_bwd_apply_kernel<false><<<grid, kThreads, 0, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, coef, N, H, W, C,
+                                                          (__nv_bfloat16*)dy, ld_dy);
+  }
+  return (int)cudaGetLastError();
+}

@@ -66,26 +66,29 @@ def _conv_impl(impl: Optional[str]) -> str:
 
 
 # ---------------------------------------------------------------------------------------------
+def _use_tc(cin: int, cout: int, impl) -> bool:
+    """tcgen05 path unless the caller asked for the library arm or the shape is unsupported."""
+    if _conv_impl(impl) == "cudnn":
+        return False
+    return bool(_ops().conv_supported(int(cin), int(cout)))
+
+
 def conv3x3_fwd(x, w, bias, y, want_stats=True, impl=None):
     """y = conv3x3(x, w) + bias; returns the BN statistics handle (see ``bn_finalize``)."""
     if _native(x):
-        if _conv_impl(impl) == "cudnn":
-            cin = w.shape[3]
-            yy = torch.nn.functional.conv2d(x[..., :cin].permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
-                                            bias.to(x.dtype), padding=1)
-            y.copy_(yy.permute(0, 2, 3, 1))
-            if not want_stats:
-                return None
-            part = torch.empty(_ops().stats_rows(), 2, y.shape[-1], dtype=torch.float32,
-                               device=y.device)
-            _ops().channel_stats(y, part)
+        cout, cin = w.shape[0], w.shape[3]
+        if _use_tc(cin, cout, impl):
+            part = _ops().conv3x3_fwd(x, w, bias, y, bool(want_stats))
             _tick()
-            return part
-        part = None
-        if want_stats:
-            part = torch.empty(_ops().stats_rows(), 2, y.shape[-1], dtype=torch.float32,
-                               device=y.device)
-        _ops().conv3x3_fwd(x, w, bias, y, part)
+            return part if want_stats else None
+        # library comparison arm (cuDNN through torch), statistics by our reduction kernel
+        yy = torch.nn.functional.conv2d(x[..., :cin].permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
+                                        bias.to(x.dtype), padding=1)
+        y.copy_(yy.permute(0, 2, 3, 1))
+        if not want_stats:
+            return None
+        part = torch.empty(_ops().stats_rows(), 2, y.shape[-1], dtype=torch.float32, device=y.device)
+        _ops().channel_stats(y, part)
         _tick()
         return part
     yy, stats = ref.conv3x3_fwd(x, w, bias, want_stats)
@@ -95,27 +98,26 @@ def conv3x3_fwd(x, w, bias, y, want_stats=True, impl=None):
 
 def conv3x3_dgrad(dy, w, dx, impl=None):
     if _native(dy):
-        if _conv_impl(impl) == "cudnn":
-            g = torch.nn.functional.conv_transpose2d(dy.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
-                                                     padding=1)
-            dx.copy_(g.permute(0, 2, 3, 1))
+        if _use_tc(w.shape[3], w.shape[0], impl):
+            _ops().conv3x3_dgrad(dy, w, dx)
+            _tick()
             return dx
-        _ops().conv3x3_dgrad(dy, w, dx)
-        _tick()
+        g = torch.nn.functional.conv_transpose2d(dy.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), padding=1)
+        dx.copy_(g.permute(0, 2, 3, 1))
         return dx
     return ref.conv3x3_dgrad(dy, w, dx)
 
 
 def conv3x3_wgrad(x, dy, dw, impl=None):
     if _native(x):
-        if _conv_impl(impl) == "cudnn":
-            cout, _, _, cin = dw.shape
-            g = torch.nn.grad.conv2d_weight(x[..., :cin].permute(0, 3, 1, 2), (cout, cin, 3, 3),
-                                            dy.permute(0, 3, 1, 2), padding=1)
-            dw.add_(g.permute(0, 2, 3, 1))
+        cout, _, _, cin = dw.shape
+        if _use_tc(cin, cout, impl) and os.environ.get("B200SEG_WGRAD", "tcgen05") != "cudnn":
+            _ops().conv3x3_wgrad(x, dy, dw)
+            _tick()
             return dw
-        _ops().conv3x3_wgrad(x, dy, dw)
-        _tick()
+        g = torch.nn.grad.conv2d_weight(x[..., :cin].permute(0, 3, 1, 2), (cout, cin, 3, 3),
+                                        dy.permute(0, 3, 1, 2), padding=1)
+        dw.add_(g.permute(0, 2, 3, 1))
         return dw
     return ref.conv3x3_wgrad(x, dy, dw)
 
@@ -151,20 +153,34 @@ def bn_relu_pool_bwd(d_out, d_pool, y, ss, gamma, dgamma, dbeta, dbias, dy):
     ref.bn_relu_pool_bwd(d_out, d_pool, y, ss, gamma, dgamma, dbeta, dbias, dy)
 
 
-def convT2x2_fwd(x, w_param, w_lp, bias, out):
+def convT2x2_fwd(x, w_param, w_lp, bias, out, impl=None):
     """``w_param``: logical (Cin,Cout,2,2) fp32 parameter; ``w_lp``: (4*Cout, Cin) kernel copy."""
     if _native(x):
-        _ops().convT2x2_fwd(x, w_lp, bias, out)
-        _tick()
+        cout4, cin = w_lp.shape
+        if _use_tc(cin, cout4 // 4, impl):
+            _ops().convT2x2_fwd(x, w_lp, bias, out)
+            _tick()
+            return
+        wl = w_lp.view(2, 2, cout4 // 4, cin).permute(3, 2, 0, 1)
+        up = torch.nn.functional.conv_transpose2d(x.permute(0, 3, 1, 2), wl, bias.to(x.dtype), stride=2)
+        out.copy_(up.permute(0, 2, 3, 1))
         return
     ref.convT2x2_fwd(x, w_param, bias, out)
 
 
 def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx):
+    """Backward of the transposed conv.  Data gradient = a stride-2 2x2 conv of d_up; weight
+    gradient = that conv's weight gradient.  (Library call for now: ~3% of the step's FLOPs.)"""
     if _native(x):
-        co = w_lp.shape[0] // 4
-        _ops().convT2x2_bwd(x, d_up, w_lp, _flat_of(dw_param).view(4 * co, -1), dbias, dx)
-        _tick(2)
+        cout4, cin = w_lp.shape
+        cout = cout4 // 4
+        wl = w_lp.view(2, 2, cout, cin).permute(3, 2, 0, 1)               # logical (Cin,Cout,2,2)
+        g = d_up.permute(0, 3, 1, 2)
+        dbias.add_(g.sum(dim=(0, 2, 3), dtype=torch.float32))
+        dwl = torch.nn.grad.conv2d_weight(g, (cin, cout, 2, 2), x.permute(0, 3, 1, 2), stride=2)
+        dw_param.add_(dwl)
+        if dx is not None:
+            dx.copy_(torch.nn.functional.conv2d(g, wl, stride=2).permute(0, 2, 3, 1))
         return
     ref.convT2x2_bwd(x, d_up, w_param, dw_param, dbias, dx)
 

@@ -1,0 +1,84 @@
+/* b200seg -- C ABI of the sm_100a kernels (lib/libb200seg.so).
+ *
+ * Every function launches on the given stream and returns a cudaError_t value as int (0 = ok).
+ * Activations are bf16 NHWC; `ld_*` is the pixel stride in elements (>= C: tensors may be
+ * channel slices of a wider buffer).  Statistics, BN vectors, parameters, gradients are fp32.
+ * "R:" cites /root/reference/"Vaihingen PyTorch 2 (кластер).py", whose stock-PyTorch op each
+ * kernel replaces (the reference itself ships no device code).
+ */
+#ifndef B200SEG_H_
+#define B200SEG_H_
+
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- BatchNorm(train) + ReLU (+ 2x2 max-pool): R:580-581, R:583-584, R:595 ------------------- */
+int b200seg_stats_rows(void);
+int b200seg_channel_stats(const void* y, long long P, int C, long long ld, float* partial, int rows,
+                          cudaStream_t st);
+int b200seg_bn_finalize(const float* partial, int rows, long long count, const float* gamma,
+                        const float* beta, float* running_mean, float* running_var, long long* nbt,
+                        float* ss, int C, float momentum, float eps, int training, cudaStream_t st);
+int b200seg_bn_relu_pool_fwd(const void* y, long long ld_y, const float* ss, void* out, long long ld_o,
+                             void* pool, long long ld_p, int N, int H, int W, int C, cudaStream_t st);
+/* workspace: float[b200seg_stats_rows()*2*C + 3*C] */
+int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, const void* d_pool, long long ld_dp,
+                             const void* y, long long ld_y, const float* ss, const float* gamma,
+                             float* dgamma, float* dbeta, void* dy, long long ld_dy, int N, int H, int W,
+                             int C, int pooled, float* workspace, cudaStream_t st);
+
+/* ---- 1x1 head + softmax cross-entropy + accuracy + head backward: R:641, R:703, R:755, R:775 -- */
+long long b200seg_head_ce_workspace_bytes(int C, int K);
+/* workspace: the last 256 bytes hold a CTA counter that must be zero before the first launch. */
+int b200seg_head_ce(const void* a, long long ld_a, const float* w, const float* bias,
+                    const unsigned char* labels, long long P, int C, int K, float grad_scale, void* da,
+                    long long ld_da, float* dw, float* db, unsigned char* pred, float* loss_acc,
+                    void* workspace, cudaStream_t st);
+
+/* ---- optimizer over the flat buffers: R:704, R:437-438, R:552-553 ------------------------------ */
+int b200seg_fused_adam(float* p, float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                       float eps, float wd, float gscale, float bc1, float bc2, void* p_lowp,
+                       int zero_grad, cudaStream_t st);
+int b200seg_fused_sgd(float* p, float* g, float* buf, long long n, float lr, float momentum, float wd,
+                      float gscale, void* p_lowp, int zero_grad, int first_step, cudaStream_t st);
+
+/* ---- gradient codecs: R:451-496 (encode), R:513-545 (decode) -----------------------------------
+ * codec: 0 fp32, 1 bf16, 2 fp16, 3 q201, 4 q21, 5 int8s, 6 fp8 */
+int b200seg_amax(const float* x, long long n, float* out, cudaStream_t st);
+int b200seg_codec_encode(const float* x, long long n, const float* scale, int codec, void* out,
+                         cudaStream_t st);
+int b200seg_codec_decode(const void* in, long long n, const float* scale, int codec, float* out,
+                         int accumulate, cudaStream_t st);
+
+/* ---- input pipeline and bilinear up-sampling: R:737-741, R:754; R:609 --------------------------- */
+int b200seg_prep_input(const unsigned char* img, long long P, int Cin, void* out, int Cpad,
+                       cudaStream_t st);
+int b200seg_upsample2x_fwd(const void* x, long long ld_x, void* out, long long ld_o, int N, int h, int w,
+                           int C, cudaStream_t st);
+int b200seg_upsample2x_bwd(const void* g, long long ld_g, void* dx, long long ld_x, int N, int h, int w,
+                           int C, cudaStream_t st);
+
+/* ---- tcgen05 / TMEM / TMA convolutions (csrc/conv): R:579, R:582 (3x3 conv), their autograd
+ * backward (dgrad, wgrad), R:607 (ConvTranspose2d k=2 s=2 fused with the concat placement, R:616).
+ * Weights are bf16 in the flat-buffer order (Cout,3,3,Cin); dgrad reads them un-transposed as an
+ * MN-major UMMA operand.  `partials` (fprop): float[rows][2][Cout] per-CTA sum / sum of squares
+ * of the bf16-rounded output, rows = b200conv_fprop_stat_rows(...). */
+int b200conv_supported(int cin, int cout);
+int b200conv_fprop_stat_rows(int N, int H, int W, int Cin, int Cout);
+int b200conv_fprop(const void* x, long long ld_x, const void* w, const float* bias, void* y,
+                   long long ld_y, int N, int H, int W, int Cin, int Cout, float* partials,
+                   cudaStream_t st);
+int b200conv_dgrad(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
+                   int H, int W, int Cin, int Cout, cudaStream_t st);
+int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                   int H, int W, int Cin, int Cout, cudaStream_t st);
+int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, const float* bias, void* out,
+                       long long ld_o, int N, int h, int w_, int Cin, int Cout, cudaStream_t st);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SEG_H_ */

@@ -1,0 +1,85 @@
+"""tcgen05 implicit-GEMM convolutions against PyTorch fp32 (the reference's own math)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from distributed_deep_learning_on_personal_computers_b200.ops import functional as Fn, reference as ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+SHAPES = [  # N, H, W, Cin, Cout
+    (2, 32, 32, 64, 64),
+    (1, 64, 48, 64, 128),
+    (2, 16, 16, 128, 256),
+    (4, 8, 8, 256, 512),
+    (1, 32, 32, 192, 64),
+    (2, 32, 32, 16, 64),       # stem: 3 channels padded to 16
+    (1, 32, 32, 32, 32),       # reference width 32
+    (1, 16, 16, 96, 32),
+    (3, 12, 20, 64, 64),       # ragged tiles
+]
+
+
+def _mk(N, H, W, Cin, Cout, seed=0):
+    torch.manual_seed(seed)
+    x = (torch.randn(N, H, W, Cin, device=DEV)).to(torch.bfloat16)
+    w = (torch.randn(Cout, 3, 3, Cin, device=DEV) * (1.0 / (3 * Cin ** 0.5))).to(torch.bfloat16)
+    b = torch.randn(Cout, device=DEV)
+    return x, w, b
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv3x3_fprop_and_stats(shape):
+    N, H, W, Cin, Cout = shape
+    x, w, b = _mk(*shape)
+    wide = torch.zeros(N, H, W, Cin + 16, dtype=torch.bfloat16, device=DEV)       # input as a channel slice
+    wide[..., :Cin] = x
+    y = torch.empty(N, H, W, Cout, dtype=torch.bfloat16, device=DEV)
+    part = Fn.conv3x3_fwd(wide[..., :Cin], w, b, y, want_stats=True, impl="tcgen05")
+    y_ref, _ = ref.conv3x3_fwd(x.float(), w.float(), b, want_stats=False)
+    torch.testing.assert_close(y.float(), y_ref, rtol=2e-2, atol=2e-2)
+    st = part.sum(0)
+    want = torch.stack([y.float().sum((0, 1, 2)), (y.float() ** 2).sum((0, 1, 2))])
+    torch.testing.assert_close(st, want, rtol=1e-3, atol=1e-1)
+
+
+@pytest.mark.parametrize("shape", [s for s in SHAPES if s[3] != 16])
+def test_conv3x3_dgrad(shape):
+    N, H, W, Cin, Cout = shape
+    _, w, _ = _mk(*shape)
+    dy = torch.randn(N, H, W, Cout, device=DEV).to(torch.bfloat16)
+    wide = torch.zeros(N, H, W, Cin + 32, dtype=torch.bfloat16, device=DEV)
+    dx = wide[..., 32:]
+    Fn.conv3x3_dgrad(dy, w, dx, impl="tcgen05")
+    dx_ref = ref.conv3x3_dgrad(dy.float(), w.float())
+    torch.testing.assert_close(dx.float(), dx_ref, rtol=2e-2, atol=3e-2)
+    assert (wide[..., :32] == 0).all()
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv3x3_wgrad(shape):
+    N, H, W, Cin, Cout = shape
+    x, w, _ = _mk(*shape)
+    dy = (torch.randn(N, H, W, Cout, device=DEV) * 0.1).to(torch.bfloat16)
+    dw = torch.ones(Cout, 3, 3, Cin, device=DEV)              # accumulates on top of existing values
+    Fn.conv3x3_wgrad(x, dy, dw, impl="tcgen05")
+    dw_ref = torch.ones(Cout, 3, 3, Cin, device=DEV)
+    ref.conv3x3_wgrad(x.float(), dy.float(), dw_ref)
+    scale = (dw_ref - 1).abs().max().item()
+    assert (dw - dw_ref).abs().max().item() <= 1e-2 * scale + 1e-3
+
+
+@pytest.mark.parametrize("N,h,w,C", [(2, 16, 16, 64), (1, 8, 8, 256), (2, 32, 32, 128), (4, 4, 4, 64)])
+def test_convT2x2_fwd_into_concat_slice(N, h, w, C):
+    torch.manual_seed(7)
+    x = torch.randn(N, h, w, C, device=DEV).to(torch.bfloat16)
+    wp = (torch.randn(C, C, 2, 2, device=DEV) * 0.05)                    # logical (Cin, Cout, 2, 2)
+    w_lp = wp.permute(2, 3, 1, 0).contiguous().view(4 * C, C).to(torch.bfloat16)
+    bias = torch.randn(C, device=DEV)
+    cat = torch.zeros(N, 2 * h, 2 * w, C + 64, dtype=torch.bfloat16, device=DEV)
+    Fn.convT2x2_fwd(x, wp, w_lp, bias, cat[..., :C], impl="tcgen05")
+    want = F.conv_transpose2d(x.float().permute(0, 3, 1, 2), w_lp.float().view(2, 2, C, C).permute(3, 2, 0, 1),
+                              bias, stride=2).permute(0, 2, 3, 1)
+    torch.testing.assert_close(cat[..., :C].float(), want, rtol=2e-2, atol=2e-2)
+    assert (cat[..., C:] == 0).all()
