@@ -1,0 +1,83 @@
+#!/usr/bin/env python
+"""Kernel-level breakdown of one training step (torch.profiler / CUPTI; times are for SHARES only).
+
+    python benchmarks/profile_step.py --impl own|reference [--conv tcgen05|cudnn] [--out FILE]
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+from torch.profiler import ProfilerActivity, profile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", default="own")
+    ap.add_argument("--conv", default="tcgen05")
+    ap.add_argument("--base-channels", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--tile", type=int, default=512)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    os.environ["B200SEG_CONV"] = a.conv
+    from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
+    tiles = synthetic_tiles(a.batch, a.tile, 6, 0)
+    if a.impl == "own":
+        from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
+        from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+        cfg = TrainConfig(base_channels=a.base_channels, tile=a.tile, batch_size=a.batch, sync_every=1, codec="fp32",
+                          world_size=1, train_tiles=a.batch, holdout_tiles=0, sample_images=0, cuda_graph=False,
+                          out_dir=os.path.join(ROOT, "gpurun_out", "prof_run"), device="cuda")
+        tr = Trainer(cfg, datasets=(tiles, None))
+        img, lab = tiles.images.cuda(), tiles.labels.cuda()
+
+        def step():
+            tr.micro_step(img, lab)
+            tr.pending = 1
+            tr.sync_and_step()
+    else:
+        from baseline.ref_loader import reference_unet
+        model = reference_unet(a.base_channels, 6).cuda().to(memory_format=torch.channels_last)
+        opt = torch.optim.Adam(model.parameters())
+        crit = torch.nn.CrossEntropyLoss()
+        torch.backends.cudnn.benchmark = True
+        x = (tiles.images.float() / 255).permute(0, 3, 1, 2).cuda().contiguous(memory_format=torch.channels_last)
+        y = tiles.labels.long().cuda()
+
+        def step():
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = crit(model(x).float(), y)
+            loss.backward()
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(a.steps):
+            step()
+        torch.cuda.synchronize()
+    rows = []
+    for ev in prof.key_averages():
+        t = getattr(ev, "device_time_total", None) or getattr(ev, "cuda_time_total", 0)
+        if t:
+            rows.append((t / a.steps / 1e3, ev.count / a.steps, ev.key))
+    rows.sort(reverse=True)
+    total = sum(r[0] for r in rows)
+    lines = [f"total kernel ms/step {total:.3f}  impl={a.impl} conv={a.conv}"]
+    for ms, cnt, name in rows[:40]:
+        lines.append(f"{ms:9.3f} ms {100 * ms / total:5.1f}%  x{cnt:6.1f}  {name[:110]}")
+    text = "\n".join(lines)
+    print(text)
+    if a.out:
+        open(a.out, "w").write(text + "\n")
+
+
+if __name__ == "__main__":
+    main()

@@ -51,7 +51,7 @@ void channel_stats(const Tensor& y, Tensor partial) {
 }
 
 void bn_finalize(const OptT& partial, int64_t count, const Tensor& gamma, const Tensor& beta,
-                 const Tensor& rmean, const Tensor& rvar, const Tensor& nbt, Tensor ss, double momentum,
+                 const OptT& conv_bias, const Tensor& rmean, const Tensor& rvar, const Tensor& nbt, Tensor ss, double momentum,
                  double eps, bool training) {
   c10::cuda::CUDAGuard g(ss.device());
   const int C = (int)gamma.numel();
@@ -59,7 +59,7 @@ void bn_finalize(const OptT& partial, int64_t count, const Tensor& gamma, const 
   TORCH_CHECK(nbt.scalar_type() == at::kLong, "num_batches_tracked must be int64");
   ok(b200seg_bn_finalize(partial.has_value() ? f32(*partial) : nullptr,
                          partial.has_value() ? (int)partial->size(0) : 0, count, f32(gamma), f32(beta),
-                         f32(rmean), f32(rvar), (long long*)nbt.data_ptr<int64_t>(), f32(ss), C,
+                         conv_bias.has_value() ? f32(*conv_bias) : nullptr, f32(rmean), f32(rvar), (long long*)nbt.data_ptr<int64_t>(), f32(ss), C,
                          (float)momentum, (float)eps, training ? 1 : 0, cur()), "bn_finalize");
 }
 
@@ -229,6 +229,31 @@ void convT2x2_fwd(const Tensor& x, const Tensor& w, const Tensor& bias, Tensor o
      "convT2x2_fwd");
 }
 
+void allreduce(at::IntArrayRef wire_ptrs, at::IntArrayRef grad_ptrs, at::IntArrayRef signal_ptrs,
+               at::IntArrayRef mult_ptrs, int64_t rank, int64_t n_elems, int64_t wire_kind, double post_scale,
+               int64_t epoch, OptT oneshot_out, int64_t blocks) {
+  const int world = (int)wire_ptrs.size();
+  TORCH_CHECK(world >= 1 && world <= 16 && (int)signal_ptrs.size() == world, "allreduce: bad pointer lists");
+  const void* wp[16]; float* gp[16]; unsigned int* sp[16]; const float* mp[16];
+  for (int r = 0; r < world; ++r) {
+    wp[r] = reinterpret_cast<const void*>(wire_ptrs[r]);
+    gp[r] = grad_ptrs.size() ? reinterpret_cast<float*>(grad_ptrs[r]) : nullptr;
+    sp[r] = reinterpret_cast<unsigned int*>(signal_ptrs[r]);
+    mp[r] = mult_ptrs.size() ? reinterpret_cast<const float*>(mult_ptrs[r]) : nullptr;
+  }
+  ok(b200seg_allreduce(wp, gp, sp, mp, (int)rank, world, n_elems, (int)wire_kind, (float)post_scale,
+                       (unsigned int)epoch, oneshot_out.has_value() ? f32(*oneshot_out) : nullptr, (int)blocks,
+                       cur()), "allreduce");
+}
+
+void write_mult(const Tensor& scale, double levels, Tensor out) {
+  c10::cuda::CUDAGuard g(out.device());
+  ok(b200seg_write_mult(f32(scale), (float)levels, f32(out), cur()), "write_mult");
+}
+
+int64_t allreduce_signal_bytes() { return b200seg_allreduce_signal_bytes(); }
+int64_t allreduce_max_blocks() { return b200seg_allreduce_max_blocks(); }
+
 bool conv_supported(int64_t cin, int64_t cout) { return b200conv_supported((int)cin, (int)cout) != 0; }
 
 }  // namespace
@@ -237,7 +262,7 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("stats_rows() -> int", &stats_rows);
   m.def("conv_supported(int cin, int cout) -> bool", &conv_supported);
   m.def("channel_stats(Tensor y, Tensor(a!) partial) -> ()", &channel_stats);
-  m.def("bn_finalize(Tensor? partial, int count, Tensor gamma, Tensor beta, Tensor(a!) running_mean, "
+  m.def("bn_finalize(Tensor? partial, int count, Tensor gamma, Tensor beta, Tensor? conv_bias, Tensor(a!) running_mean, "
         "Tensor(b!) running_var, Tensor(c!) num_batches_tracked, Tensor(d!) ss, float momentum, float eps, "
         "bool training) -> ()", &bn_finalize);
   m.def("bn_relu_pool_fwd(Tensor y, Tensor ss, Tensor(a!) out, Tensor(b!)? pool) -> ()", &bn_relu_pool_fwd);
@@ -257,6 +282,11 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("prep_input(Tensor img, Tensor(a!) out) -> ()", &prep_input);
   m.def("upsample_bilinear2x_fwd(Tensor x, Tensor(a!) out) -> ()", &upsample_fwd);
   m.def("upsample_bilinear2x_bwd(Tensor d_up, Tensor(a!) dx) -> ()", &upsample_bwd);
+  m.def("allreduce(int[] wire_ptrs, int[] grad_ptrs, int[] signal_ptrs, int[] mult_ptrs, int rank, int n_elems, "
+        "int wire_kind, float post_scale, int epoch, Tensor(a!)? oneshot_out, int blocks) -> ()", &allreduce);
+  m.def("write_mult(Tensor scale, float levels, Tensor(a!) out) -> ()", &write_mult);
+  m.def("allreduce_signal_bytes() -> int", &allreduce_signal_bytes);
+  m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);
   m.def("conv3x3_dgrad(Tensor dy, Tensor w, Tensor(a!) dx) -> ()", &conv3x3_dgrad);
   m.def("conv3x3_wgrad(Tensor x, Tensor dy, Tensor(a!) dw) -> ()", &conv3x3_wgrad);

@@ -1,0 +1,212 @@
+// Gradient all-reduce over NVLink peer memory (no NCCL on this path).
+//
+// Replaces the reference's whole exchange round: quantize -> D2H -> pickle -> gzip -> TCP to the
+// server, reduce at the root, re-quantize, broadcast, dequantize (grad_serv_mean R:255-440,
+// grad_client_mean R:443-556).  On an NVSwitch box every GPU reaches every peer
+// at full bandwidth, so the star is the wrong shape; each rank maps all peers' buffers
+// ("symmetric memory", handles exchanged once at start-up) and the kernels below read / write
+// them directly:
+//
+//   two-shot (bandwidth-optimal, in place): rank r owns slice r.  It loads slice r of EVERY rank's
+//     wire buffer (peer loads), dequantizes on load, accumulates in fp32 in fixed rank order
+//     (=> bit-identical result on all ranks, the reference's R:402-433 guarantee), applies the
+//     1/world (and 1/K) scale, and stores the result into slice r of EVERY rank's fp32 gradient
+//     buffer (peer stores).  Traffic per GPU: (W-1)/W of the wire size in, (W-1)/W * 4 B out.
+//   one-shot (latency-optimal, small buffers): every rank loads everything from everyone and
+//     reduces locally into a private output.
+//
+// Cross-GPU ordering uses per-CTA flags in a symmetric signal pad: st.release.sys to the peer,
+// ld.acquire.sys spin (bounded, then trap) on the local pad, with a monotonically increasing
+// epoch so pads never need clearing.
+#include "../common.cuh"
+#include "b200seg.h"
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+
+namespace b200 {
+
+constexpr int kMaxRanks = 16;
+constexpr int kArThreads = 512;
+
+struct PeerPtrs {
+  const void* wire[kMaxRanks];     // each rank's wire-format gradient buffer
+  float* grad[kMaxRanks];          // each rank's fp32 gradient buffer (two-shot destination)
+  uint32_t* signal[kMaxRanks];     // each rank's signal pad: [max_blocks][kMaxRanks]
+  const float* mult[kMaxRanks];    // each rank's dequantization multiplier (device, symmetric); NULL = 1
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Every CTA b of every rank meets CTA b of all other ranks.
+__device__ __forceinline__ void cross_gpu_barrier(const PeerPtrs& pp, int rank, int world, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const int peer = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(pp.signal[peer] + (size_t)blockIdx.x * kMaxRanks + rank, epoch);
+    const uint32_t* mine = pp.signal[rank] + (size_t)blockIdx.x * kMaxRanks + peer;
+    long long spins = 0;
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (++spins > (1ll << 31)) { asm volatile("trap;"); }
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T> struct Wire;
+template <> struct Wire<float> {
+  static constexpr int kVec = 4;   // elements per 16 bytes
+  __device__ static void load(const void* p, size_t i, float (&f)[16 / sizeof(float)]) {
+    float4 v = reinterpret_cast<const float4*>(p)[i];
+    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+  }
+};
+template <> struct Wire<__nv_bfloat16> {
+  static constexpr int kVec = 8;
+  __device__ static void load(const void* p, size_t i, float (&f)[8]) {
+    unpack8(reinterpret_cast<const bf16x8*>(p)[i], f);
+  }
+};
+template <> struct Wire<__half> {
+  static constexpr int kVec = 8;
+  __device__ static void load(const void* p, size_t i, float (&f)[8]) {
+    uint4 v = reinterpret_cast<const uint4*>(p)[i];
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { float2 t = __half22float2(h[j]); f[2 * j] = t.x; f[2 * j + 1] = t.y; }
+  }
+};
+template <> struct Wire<int8_t> {
+  static constexpr int kVec = 16;
+  __device__ static void load(const void* p, size_t i, float (&f)[16]) {
+    uint4 v = reinterpret_cast<const uint4*>(p)[i];
+    const int8_t* b = reinterpret_cast<const int8_t*>(&v);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = (float)b[j];
+  }
+};
+template <> struct Wire<__nv_fp8_e4m3> {
+  static constexpr int kVec = 16;
+  __device__ static void load(const void* p, size_t i, float (&f)[16]) {
+    uint4 v = reinterpret_cast<const uint4*>(p)[i];
+    const __nv_fp8_e4m3* b = reinterpret_cast<const __nv_fp8_e4m3*>(&v);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = float(b[j]);
+  }
+};
+
+// n_vec = number of 16-byte wire vectors in the whole buffer (the buffer is padded to that).
+template <typename T, bool ONESHOT>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_kernel(PeerPtrs pp, int rank, int world, size_t n_vec, float post_scale, uint32_t epoch,
+                 float* __restrict__ oneshot_out) {
+  constexpr int V = Wire<T>::kVec;
+  cross_gpu_barrier(pp, rank, world, epoch);           // every rank's wire buffer is complete
+  float mult[kMaxRanks];
+#pragma unroll
+  for (int r = 0; r < kMaxRanks; ++r)
+    mult[r] = (r < world && pp.mult[r] != nullptr) ? *reinterpret_cast<const volatile float*>(pp.mult[r]) : 1.f;
+  size_t v0 = 0, v1 = n_vec;
+  if (!ONESHOT) {
+    const size_t per = (n_vec + world - 1) / world;
+    v0 = (size_t)rank * per;
+    v1 = v0 + per < n_vec ? v0 + per : n_vec;
+  }
+  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {              // fixed order: identical bits on every rank
+      if (r >= world) break;
+      float f[V];
+      Wire<T>::load(pp.wire[r], i, f);
+      const float m = mult[r];
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] = fmaf(f[j], m, acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] *= post_scale;
+    if (ONESHOT) {
+#pragma unroll
+      for (int q = 0; q < V / 4; ++q)
+        reinterpret_cast<float4*>(oneshot_out)[i * (V / 4) + q] =
+            make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+    } else {
+      for (int r = 0; r < world; ++r) {
+        const int dst = (rank + r) % world;            // stagger the peers
+#pragma unroll
+        for (int q = 0; q < V / 4; ++q)
+          reinterpret_cast<float4*>(pp.grad[dst])[i * (V / 4) + q] =
+              make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+      }
+    }
+  }
+  if (!ONESHOT) cross_gpu_barrier(pp, rank, world, epoch + 1);   // all slices have landed everywhere
+}
+
+template <typename T>
+static int launch_ar(const PeerPtrs& pp, int rank, int world, size_t n_elems, float post_scale,
+                     uint32_t epoch, float* oneshot_out, int blocks, cudaStream_t st) {
+  const size_t n_vec = n_elems / Wire<T>::kVec;
+  if (oneshot_out != nullptr)
+    allreduce_kernel<T, true><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, oneshot_out);
+  else
+    allreduce_kernel<T, false><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, nullptr);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace b200
+
+namespace b200 {
+__global__ void write_mult_kernel(const float* scale, float levels, float* out) {
+  *out = (levels > 0.f) ? __fdiv_rn(*scale, levels) : 1.f;
+}
+}  // namespace b200
+
+using namespace b200;
+
+// out[0] = scale / levels (levels <= 0: 1): the multiplier peers apply to this rank's wire buffer.
+extern "C" int b200seg_write_mult(const float* scale, float levels, float* out, cudaStream_t st) {
+  write_mult_kernel<<<1, 1, 0, st>>>(scale, levels, out);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200seg_allreduce_max_blocks() { return 64; }
+extern "C" long long b200seg_allreduce_signal_bytes() {
+  return (long long)b200seg_allreduce_max_blocks() * kMaxRanks * sizeof(uint32_t);
+}
+
+// wire_kind: 0 fp32, 1 bf16, 2 fp16 (also q201), 3 int8 (q21, int8s), 4 fp8.  n_elems must be a
+// multiple of 16.  oneshot_out == NULL selects the in-place two-shot algorithm.  Two epochs are
+// consumed per call: pass epoch = 2 * call_index + 1.
+extern "C" int b200seg_allreduce(const void* const* wire_ptrs, float* const* grad_ptrs,
+                                 unsigned int* const* signal_ptrs, const float* const* mult_ptrs, int rank, int world,
+                                 long long n_elems, int wire_kind, float post_scale, unsigned int epoch,
+                                 float* oneshot_out, int blocks, cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || (n_elems % 16) || blocks < 1 || blocks > b200seg_allreduce_max_blocks())
+    return (int)cudaErrorInvalidValue;
+  PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) {
+    pp.wire[r] = wire_ptrs[r];
+    pp.grad[r] = grad_ptrs ? grad_ptrs[r] : nullptr;
+    pp.signal[r] = signal_ptrs[r];
+    pp.mult[r] = mult_ptrs ? mult_ptrs[r] : nullptr;
+  }
+  switch (wire_kind) {
+    case 0: return launch_ar<float>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
+    case 1: return launch_ar<__nv_bfloat16>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
+    case 2: return launch_ar<__half>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
+    case 3: return launch_ar<int8_t>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
+    case 4: return launch_ar<__nv_fp8_e4m3>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
+  }
+  return (int)cudaErrorInvalidValue;
+}

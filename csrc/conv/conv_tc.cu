@@ -78,6 +78,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
   __shared__ __align__(8) uint64_t bar_tfull[2], bar_tempty[2];
   __shared__ uint32_t tmem_base_s;
+  __shared__ float s_bias[256];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -95,6 +96,12 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
+  if (p.bias != nullptr) {
+    for (int c = threadIdx.x; c < p.block_n; c += kConvThreads) {
+      const int col = (blockIdx.x % p.n_tiles) * p.block_n + c;
+      s_bias[c] = (col < p.n_total) ? p.bias[p.out_mode == 1 ? (col % p.convt_cout) : col] : 0.f;
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -175,11 +182,18 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const uint32_t row_bytes = ocb * 2;
     const uint32_t swz_mask = (row_bytes >> 4) - 1;       // 16-byte chunks per row - 1
     const uint32_t group_bytes = 128 * row_bytes;
-    float st_s[kMaxGroups], st_q[kMaxGroups];
+    // statistics: this thread owns ONE 16-byte chunk column (8 channels) of the N tile and walks
+    // CPR of the 128 rows; requires block_n / 8 to divide 128 (power-of-two Cout).
+    const int cpr = p.block_n >> 3;                       // chunks per row
+    const int st_cc = et % cpr;                           // my chunk column
+    const int st_rg = et / cpr;                           // my row group
+    const int st_rstep = 128 / cpr;
+    const int st_grp = (st_cc * 8) >> ocb_log2;
+    const uint32_t st_chunk = ((st_cc * 8) & (ocb - 1)) >> 3;
+    float st_s[8], st_q[8];
 #pragma unroll
-    for (int g = 0; g < kMaxGroups; ++g) st_s[g] = st_q[g] = 0.f;
-    const int st_c = et & (ocb - 1);                      // channel (within a group) for statistics
-    const int st_r0 = (et >> ocb_log2) * ocb;             // first of the `ocb` rows this thread sums
+    for (int j = 0; j < 8; ++j) st_s[j] = st_q[j] = 0.f;
+    const bool has_bias = p.bias != nullptr;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int m = m_first; m < p.m_tiles; m += m_step) {
@@ -202,19 +216,15 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
         tmem_ld_wait();
         const int ncols = (p.block_n - c0 >= 32) ? 32 : 16;
-        const int col0 = n_tile * p.block_n + c0;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {                     // four 16-byte chunks of 8 channels
           if (v * 8 < ncols) {
             float f[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float b = 0.f;
-              if (p.bias != nullptr) {
-                const int col = col0 + v * 8 + j;
-                b = __ldg(p.bias + (p.out_mode == 1 ? (col % p.convt_cout) : col));
-              }
-              f[j] = __uint_as_float(r[v * 8 + j]) + b;
+            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+            if (has_bias) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[j] += s_bias[c0 + v * 8 + j];
             }
             const int cg = c0 + v * 8;                    // column within the N tile
             const int grp = cg >> ocb_log2;
@@ -232,25 +242,23 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       named_bar_sync(1, 128);
       if (p.partials != nullptr) {
         const bool full_tile = (w0 + TW <= p.W) && (h0 + TH <= p.H) && (n0 + p.tn <= p.N);
-        for (int g = 0; g < p.groups; ++g) {
-          float s = 0.f, q = 0.f;
-          const uint8_t* gb = staging + g * group_bytes;
-          for (int i = 0; i < ocb; ++i) {
-            const int rr = st_r0 + i;
-            bool valid = true;
-            if (!full_tile) {
-              const int tw_ = rr & (TW - 1), th_ = (rr >> p.tw_log2) & (TH - 1), tn_ = rr >> (p.tw_log2 + p.th_log2);
-              valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
-            }
-            const uint32_t off = rr * row_bytes + ((st_c >> 3) << 4);
-            const uint32_t phys = (off ^ (((off >> 7) & swz_mask) << 4)) + (st_c & 7) * 2;
-            const float v = valid ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + phys)) : 0.f;
-            s += v;
-            q = fmaf(v, v, q);
+        const uint8_t* gb = staging + st_grp * group_bytes;
+#pragma unroll 4
+        for (int i = 0; i < cpr; ++i) {
+          const int rr = st_rg + i * st_rstep;
+          bool valid = true;
+          if (!full_tile) {
+            const int tw_ = rr & (TW - 1), th_ = (rr >> p.tw_log2) & (TH - 1), tn_ = rr >> (p.tw_log2 + p.th_log2);
+            valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
           }
+          const uint32_t off = rr * row_bytes + (st_chunk << 4);
+          const uint32_t phys = off ^ (((off >> 7) & swz_mask) << 4);
+          float f[8];
+          unpack8(*reinterpret_cast<const bf16x8*>(gb + phys), f);
+          if (valid) {
 #pragma unroll
-          for (int gg = 0; gg < kMaxGroups; ++gg)
-            if (gg == g) { st_s[gg] += s; st_q[gg] += q; }
+            for (int j = 0; j < 8; ++j) { st_s[j] += f[j]; st_q[j] = fmaf(f[j], f[j], st_q[j]); }
+          }
         }
       }
       if (et == 0) {
@@ -269,22 +277,18 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       named_bar_sync(1, 128);
     }
     if (p.partials != nullptr) {
-      // combine the (128 / ocb) threads that share a channel, then one row of partials per CTA
-      float* red = reinterpret_cast<float*>(staging);    // [128/ocb][2][groups*ocb]
-      const int tpc = 128 >> ocb_log2;
-      const int ncol = p.groups * ocb;
-      for (int g = 0; g < p.groups; ++g) {
-        float s = 0.f, q = 0.f;
+      // combine the (128 / cpr) threads that share a chunk column, then one row of partials per CTA
+      float* red = reinterpret_cast<float*>(staging);    // [128/cpr][2][block_n]
+      const int ncol = p.block_n;
 #pragma unroll
-        for (int gg = 0; gg < kMaxGroups; ++gg)
-          if (gg == g) { s = st_s[gg]; q = st_q[gg]; }
-        red[((et >> ocb_log2) * 2 + 0) * ncol + g * ocb + st_c] = s;
-        red[((et >> ocb_log2) * 2 + 1) * ncol + g * ocb + st_c] = q;
+      for (int j = 0; j < 8; ++j) {
+        red[(st_rg * 2 + 0) * ncol + st_cc * 8 + j] = st_s[j];
+        red[(st_rg * 2 + 1) * ncol + st_cc * 8 + j] = st_q[j];
       }
       named_bar_sync(1, 128);
       for (int c = et; c < ncol; c += 128) {
         float s = 0.f, q = 0.f;
-        for (int i = 0; i < tpc; ++i) { s += red[(i * 2 + 0) * ncol + c]; q += red[(i * 2 + 1) * ncol + c]; }
+        for (int i = 0; i < st_rstep; ++i) { s += red[(i * 2 + 0) * ncol + c]; q += red[(i * 2 + 1) * ncol + c]; }
         const int col = n_tile * p.block_n + c;
         if (col < p.n_total) {
           p.partials[((size_t)m_first * 2 + 0) * p.n_total + col] = s;
@@ -551,13 +555,14 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if (mode == 2 && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.bias = bias;
   p.partials = partials;
+  if (partials != nullptr && (128 % (p.block_n / 8) != 0)) return (int)cudaErrorInvalidValue;
   p.a_bytes = 128 * BK * 2;
   const bool bmn = (mode == 1);
   const uint32_t b_raw = bmn ? (uint32_t)((p.block_n + 63) / 64) * 64 * BK * 2 : (uint32_t)p.block_n * BK * 2;
   p.b_bytes = b_raw;
   p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
   p.staging_bytes = 128u * p.block_n * 2;
-  if (p.staging_bytes < 4096) p.staging_bytes = 4096;
+  if (p.staging_bytes < 8192) p.staging_bytes = 8192;
   int stages = (int)((kSmemBudget - p.staging_bytes) / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return (int)cudaErrorInvalidValue;

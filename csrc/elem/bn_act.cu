@@ -54,33 +54,48 @@ channel_stats_kernel(const __nv_bfloat16* __restrict__ y, long long P, int C, lo
 // ---------------------------------------------------------------------------------------------
 // partial[R][2][C] -> ss[4][C] = scale, shift, mean, invstd; running stats (momentum, unbiased
 // variance) and num_batches_tracked as nn.BatchNorm2d (R:580).
+// One warp per channel.  `conv_bias`: the bias of the conv that produced y.  The conv kernels do
+// NOT add it: in training mode it cancels inside the normalisation (it only shifts the running
+// mean), in eval mode it is folded into `shift`.
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
 __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, long long count,
                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   const float* __restrict__ conv_bias,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    long long* __restrict__ nbt, float* __restrict__ ss, int C,
                                    float momentum, float eps, int training) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= C) return;
+  const double cb = conv_bias != nullptr ? (double)conv_bias[c] : 0.0;
   double mean, var;
   if (training) {
     double s = 0.0, q = 0.0;
-    for (int r = 0; r < rows; ++r) {
+    for (int r = lane; r < rows; r += 32) {
       s += (double)partial[((size_t)r * 2 + 0) * C + c];
       q += (double)partial[((size_t)r * 2 + 1) * C + c];
     }
+    s = warp_sum_d(s);
+    q = warp_sum_d(q);
     mean = s / (double)count;
     var = q / (double)count - mean * mean;
     if (var < 0.0) var = 0.0;
-    if (running_mean != nullptr) {
+    if (lane == 0 && running_mean != nullptr) {
       double unb = var * ((double)count / (double)(count > 1 ? count - 1 : 1));
-      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * (mean + cb));
       running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unb);
     }
-    if (c == 0 && nbt != nullptr) *nbt += 1;
+    if (c == 0 && lane == 0 && nbt != nullptr) *nbt += 1;
   } else {
-    mean = (double)running_mean[c];
+    mean = (double)running_mean[c] - cb;          // statistics of the bias-free conv output
     var = (double)running_var[c];
   }
+  if (lane != 0) return;
   const double invstd = rsqrt(var + (double)eps);
   const double scale = (double)gamma[c] * invstd;
   ss[0 * C + c] = (float)scale;
@@ -260,13 +275,17 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
                                        const float* __restrict__ gamma, const float* __restrict__ ss,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ coef, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (c >= C) return;
   double sg = 0.0, sgx = 0.0;
-  for (int r = 0; r < rows; ++r) {
+  for (int r = lane; r < rows; r += 32) {
     sg += (double)partial[((size_t)r * 2 + 0) * C + c];
     sgx += (double)partial[((size_t)r * 2 + 1) * C + c];
   }
+  sg = warp_sum_d(sg);
+  sgx = warp_sum_d(sgx);
+  if (lane != 0) return;
   dbeta[c] += (float)sg;
   dgamma[c] += (float)sgx;
   const double mean = ss[2 * C + c], inv = ss[3 * C + c];
@@ -340,11 +359,11 @@ extern "C" int b200seg_channel_stats(const void* y, long long P, int C, long lon
 }
 
 extern "C" int b200seg_bn_finalize(const float* partial, int rows, long long count, const float* gamma,
-                                   const float* beta, float* running_mean, float* running_var,
-                                   long long* nbt, float* ss, int C, float momentum, float eps,
-                                   int training, cudaStream_t st) {
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, count, gamma, beta, running_mean,
-                                                      running_var, nbt, ss, C, momentum, eps, training);
+                                   const float* beta, const float* conv_bias, float* running_mean,
+                                   float* running_var, long long* nbt, float* ss, int C, float momentum,
+                                   float eps, int training, cudaStream_t st) {
+  bn_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, count, gamma, beta, conv_bias, running_mean,
+                                                  running_var, nbt, ss, C, momentum, eps, training);
   return (int)cudaGetLastError();
 }
 
@@ -387,7 +406,7 @@ extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, cons
   } else {
     bn_bwd_reduce_kernel<false><<<rows, kThreads, smem, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, N, H, W, C, partial);
   }
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
+  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
   if (pooled) {
     int grid = grid_for(P / 4 * CV, kThreads);
     bn_bwd_apply_kernel<true><<<grid, kThreads, 0, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, coef, N, H, W, C,

@@ -169,13 +169,15 @@ class NativeEngine:
         sp = st.spec
         w = self._w3(self.flat_lp, sp.name + ".weight")
         bias = self._seg(self.flat_p, sp.name + ".bias")
-        st.stats = Fn.conv3x3_fwd(st.x, w, bias, st.y, want_stats=self.training,
+        # the conv bias is NOT added by the conv: BatchNorm absorbs it (see ops.reference.bn_finalize)
+        st.stats = Fn.conv3x3_fwd(st.x, w, None, st.y, want_stats=self.training,
                                   impl=self.conv_impl)
         bn = sp.bn
         Fn.bn_finalize(st.stats, st.y.shape[0] * st.y.shape[1] * st.y.shape[2],
                        self._seg(self.flat_p, bn + ".weight"), self._seg(self.flat_p, bn + ".bias"),
                        self._buffers[bn + ".running_mean"], self._buffers[bn + ".running_var"],
-                       self._buffers[bn + ".num_batches_tracked"], st.ss, training=self.training)
+                       self._buffers[bn + ".num_batches_tracked"], st.ss, training=self.training,
+                       conv_bias=bias)
         Fn.bn_relu_pool_fwd(st.y, st.ss, st.out, st.pool)
 
     def _stage_bwd(self, st: _Stage, need_dx: bool = True) -> None:

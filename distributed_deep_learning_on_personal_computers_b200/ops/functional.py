@@ -83,7 +83,7 @@ def conv3x3_fwd(x, w, bias, y, want_stats=True, impl=None):
             return part if want_stats else None
         # library comparison arm (cuDNN through torch), statistics by our reduction kernel
         yy = torch.nn.functional.conv2d(x[..., :cin].permute(0, 3, 1, 2), w.permute(0, 3, 1, 2),
-                                        bias.to(x.dtype), padding=1)
+                                        None if bias is None else bias.to(x.dtype), padding=1)
         y.copy_(yy.permute(0, 2, 3, 1))
         if not want_stats:
             return None
@@ -123,14 +123,14 @@ def conv3x3_wgrad(x, dy, dw, impl=None):
 
 
 def bn_finalize(stats, count, gamma, beta, running_mean, running_var, num_batches_tracked, ss,
-                momentum=0.1, eps=1e-5, training=True):
+                momentum=0.1, eps=1e-5, training=True, conv_bias=None):
     if _native(ss):
-        _ops().bn_finalize(stats, int(count), gamma, beta, running_mean, running_var,
+        _ops().bn_finalize(stats, int(count), gamma, beta, conv_bias, running_mean, running_var,
                            num_batches_tracked, ss, float(momentum), float(eps), bool(training))
         _tick()
         return ss
     out = ref.bn_finalize(stats, count, gamma, beta, running_mean, running_var, momentum, eps,
-                          training)
+                          training, conv_bias)
     if training:
         num_batches_tracked.add_(1)
     ss.copy_(out)

@@ -77,19 +77,24 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, accumulat
 # with momentum 0.1 and the unbiased variance, as nn.BatchNorm2d does (R:580).
 def bn_finalize(stats: torch.Tensor, count: int, gamma: torch.Tensor, beta: torch.Tensor,
                 running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
-                momentum: float = 0.1, eps: float = 1e-5, training: bool = True
-                ) -> torch.Tensor:
-    """Returns fp32 (4, C): scale, shift, mean, invstd."""
+                momentum: float = 0.1, eps: float = 1e-5, training: bool = True,
+                conv_bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Returns fp32 (4, C): scale, shift, mean, invstd.
+
+    ``conv_bias`` is the bias of the conv that produced ``y`` when that conv did NOT add it (the
+    engine's convention): in training mode a per-channel constant cancels inside the
+    normalisation and only shifts the running mean; in eval mode it is folded into ``shift``."""
+    cb = 0.0 if conv_bias is None else conv_bias.to(torch.float64)
     if training:
         s = stats.to(torch.float64)
         mean = s[0] / count
         var = (s[1] / count - mean * mean).clamp_(min=0.0)
         if running_mean is not None:
             unbiased = var * (count / max(count - 1, 1))
-            running_mean.mul_(1 - momentum).add_(mean.to(running_mean.dtype), alpha=momentum)
+            running_mean.mul_(1 - momentum).add_((mean + cb).to(running_mean.dtype), alpha=momentum)
             running_var.mul_(1 - momentum).add_(unbiased.to(running_var.dtype), alpha=momentum)
     else:
-        mean = running_mean.to(torch.float64)
+        mean = running_mean.to(torch.float64) - cb
         var = running_var.to(torch.float64)
     invstd = torch.rsqrt(var + eps)
     scale = gamma.to(torch.float64) * invstd

@@ -1,0 +1,118 @@
+"""Symmetric-memory all-reduce: the Python side of ``csrc/comm/allreduce.cu``.
+
+The reference's rendezvous opens one TCP connection per worker (``create_server`` /
+``create_worker``, ``R:173-206``) and every later exchange goes through the root.  Here the
+rendezvous exchanges *memory handles*: each rank allocates its gradient buffer, its wire buffer
+and a signal pad from CUDA's peer-shareable allocator (``torch.distributed._symmetric_memory``
+does the handle exchange over the existing process group) and maps every peer's copies into its
+own address space.  After that the gradient exchange is one kernel launch per step with no host
+involvement, no NCCL, and no root.
+
+``SymmetricAllReduce.buffer`` is the flat fp32 gradient buffer the engine accumulates into
+(``Trainer`` re-homes ``.grad`` there).  ``all_reduce_()`` leaves the rank-order fp32 sum of all
+replicas in it on every rank, bit-identical.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from .codecs import Codec
+from .dist import DistContext
+
+_WIRE_KIND = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2, torch.int8: 3}
+ONESHOT_MAX_BYTES = 512 * 1024
+
+
+def available(ctx: DistContext) -> bool:
+    """Native path needs CUDA, NCCL process group (for the handle exchange), P2P between all ranks
+    of the node, and the library."""
+    if ctx.device.type != "cuda" or ctx.world_size < 2 or ctx.world_size > 16:
+        return False
+    from ..ops import loader
+    if loader.library() is None:
+        return False
+    try:
+        import torch.distributed._symmetric_memory  # noqa: F401
+    except Exception:
+        return False
+    n = torch.cuda.device_count()
+    if n < ctx.world_size:
+        return False
+    me = ctx.device.index
+    return all(torch.cuda.can_device_access_peer(me, d) for d in range(n) if d != me)
+
+
+class SymmetricAllReduce:
+    def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.ctx, self.codec = ctx, codec
+        self.group = group or dist.group.WORLD
+        dev = like_flat.device
+        n = like_flat.numel()
+        self.n = (n + 63) // 64 * 64
+        self.buffer_full = symm_mem.empty(self.n, dtype=torch.float32, device=dev)
+        self.buffer_full.zero_()
+        self.buffer = self.buffer_full[:n]
+        self.h_grad = symm_mem.rendezvous(self.buffer_full, self.group)
+        ops = torch.ops.b200seg
+        sig_words = ops.allreduce_signal_bytes() // 4 + 64
+        self.signal = symm_mem.empty(sig_words, dtype=torch.int32, device=dev)
+        self.signal.zero_()
+        self.h_sig = symm_mem.rendezvous(self.signal, self.group)
+        self.mult_off = ops.allreduce_signal_bytes()            # float slot after the flags
+        self.mult_slot = self.signal.view(torch.float32)[self.mult_off // 4:self.mult_off // 4 + 1]
+        self.mult_slot.fill_(1.0)
+        self.wire = None
+        self.h_wire = None
+        fp8 = getattr(torch, "float8_e4m3fn", None)
+        if codec.name != "fp32":
+            self.wire = symm_mem.empty(self.n * codec.wire_bytes, dtype=torch.uint8, device=dev)
+            self.wire.zero_()
+            self.h_wire = symm_mem.rendezvous(self.wire, self.group)
+            self.wire_kind = 4 if (fp8 is not None and codec.wire_dtype == fp8) else _WIRE_KIND[codec.wire_dtype]
+        else:
+            self.wire_kind = 0
+        self.grad_ptrs = [int(p) for p in self.h_grad.buffer_ptrs]
+        self.sig_ptrs = [int(p) for p in self.h_sig.buffer_ptrs]
+        self.wire_ptrs = [int(p) for p in self.h_wire.buffer_ptrs] if self.h_wire else self.grad_ptrs
+        self.mult_ptrs = [p + self.mult_off for p in self.sig_ptrs] if codec.needs_scale else []
+        self.calls = 0
+        self.blocks = int(ops.allreduce_max_blocks())
+        self.oneshot_out: Optional[torch.Tensor] = None
+        if self.n * 4 <= ONESHOT_MAX_BYTES:
+            self.oneshot_out = torch.empty(self.n, dtype=torch.float32, device=dev)
+        torch.cuda.synchronize(dev)
+        dist.barrier(device_ids=[dev.index])
+
+    @property
+    def multicast_supported(self) -> bool:
+        try:
+            return bool(self.h_grad.has_multicast_support)
+        except Exception:
+            return False
+
+    @torch.no_grad()
+    def all_reduce_(self, post_scale: float = 1.0) -> torch.Tensor:
+        """Sum over ranks (times ``post_scale``) into ``buffer`` on every rank."""
+        from ..ops import functional as Fn
+        ops = torch.ops.b200seg
+        c = self.codec
+        if c.name != "fp32":
+            scale = Fn.codec_amax(self.buffer_full) if c.needs_scale else torch.ones((), device=self.buffer.device)
+            ops.codec_encode(self.buffer_full, scale, self.wire, c.name)
+            Fn._tick()
+            if c.needs_scale:
+                levels = c.levels if c.levels is not None else 448.0
+                ops.write_mult(scale, float(levels), self.mult_slot)
+                Fn._tick()
+        epoch = 2 * self.calls + 1
+        self.calls += 1
+        ops.allreduce(self.wire_ptrs, self.grad_ptrs, self.sig_ptrs, self.mult_ptrs, self.ctx.rank, self.n,
+                      self.wire_kind, float(post_scale), epoch, self.oneshot_out, self.blocks)
+        Fn._tick()
+        if self.oneshot_out is not None:
+            self.buffer_full.copy_(self.oneshot_out)
+        return self.buffer

@@ -19,9 +19,11 @@ extern "C" {
 int b200seg_stats_rows(void);
 int b200seg_channel_stats(const void* y, long long P, int C, long long ld, float* partial, int rows,
                           cudaStream_t st);
+/* conv_bias: bias of the producing conv (may be NULL); the conv kernels never add it, see bn_act.cu */
 int b200seg_bn_finalize(const float* partial, int rows, long long count, const float* gamma,
-                        const float* beta, float* running_mean, float* running_var, long long* nbt,
-                        float* ss, int C, float momentum, float eps, int training, cudaStream_t st);
+                        const float* beta, const float* conv_bias, float* running_mean,
+                        float* running_var, long long* nbt, float* ss, int C, float momentum, float eps,
+                        int training, cudaStream_t st);
 int b200seg_bn_relu_pool_fwd(const void* y, long long ld_y, const float* ss, void* out, long long ld_o,
                              void* pool, long long ld_p, int N, int H, int W, int C, cudaStream_t st);
 /* workspace: float[b200seg_stats_rows()*2*C + 3*C] */
@@ -60,6 +62,19 @@ int b200seg_upsample2x_fwd(const void* x, long long ld_x, void* out, long long l
                            int C, cudaStream_t st);
 int b200seg_upsample2x_bwd(const void* g, long long ld_g, void* dx, long long ld_x, int N, int h, int w,
                            int C, cudaStream_t st);
+
+/* ---- gradient all-reduce over NVLink peer memory: R:255-440, R:443-556 -------------------------
+ * Pointer arrays are indexed by rank and hold addresses valid in THIS process (symmetric memory).
+ * wire_kind: 0 fp32, 1 bf16, 2 fp16 (also q201), 3 int8 (q21, int8s), 4 fp8.  n_elems % 16 == 0.
+ * oneshot_out == NULL: in-place two-shot into every rank's grad buffer; else one-shot into
+ * oneshot_out.  Two epochs are consumed per call: pass epoch = 2 * call_index + 1. */
+int b200seg_allreduce_max_blocks(void);
+long long b200seg_allreduce_signal_bytes(void);
+int b200seg_write_mult(const float* scale, float levels, float* out, cudaStream_t st);
+int b200seg_allreduce(const void* const* wire_ptrs, float* const* grad_ptrs,
+                      unsigned int* const* signal_ptrs, const float* const* mult_ptrs, int rank, int world,
+                      long long n_elems, int wire_kind, float post_scale, unsigned int epoch,
+                      float* oneshot_out, int blocks, cudaStream_t st);
 
 /* ---- tcgen05 / TMEM / TMA convolutions (csrc/conv): R:579, R:582 (3x3 conv), their autograd
  * backward (dgrad, wgrad), R:607 (ConvTranspose2d k=2 s=2 fused with the concat placement, R:616).
