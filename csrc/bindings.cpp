@@ -254,6 +254,22 @@ void write_mult(const Tensor& scale, double levels, Tensor out) {
 int64_t allreduce_signal_bytes() { return b200seg_allreduce_signal_bytes(); }
 int64_t allreduce_max_blocks() { return b200seg_allreduce_max_blocks(); }
 
+void convT2x2_bwd(const Tensor& x, const Tensor& d_up, const Tensor& w, Tensor dw, OptT dx) {
+  c10::cuda::CUDAGuard g(x.device());
+  bf16(x, "x"); bf16(d_up, "d_up"); bf16(w, "w");
+  const int Cin = (int)w.size(1), Cout = (int)w.size(0) / 4;
+  TORCH_CHECK(dw.is_contiguous() && dw.scalar_type() == at::kFloat && dw.size(0) == 4 * Cout && dw.size(1) == Cin,
+              "dw must be fp32 (4*Cout, Cin) contiguous");
+  const int N = (int)x.size(0), h = (int)x.size(1), w_ = (int)x.size(2);
+  ok(b200conv_convT_wgrad(x.data_ptr(), nhwc_ld(x, "x"), d_up.data_ptr(), nhwc_ld(d_up, "d_up"), dw.data_ptr<float>(),
+                          N, h, w_, Cin, Cout, cur()), "convT2x2_wgrad");
+  if (dx.has_value()) {
+    bf16(*dx, "dx");
+    ok(b200conv_convT_dgrad(d_up.data_ptr(), nhwc_ld(d_up, "d_up"), w.data_ptr(), dx->data_ptr(), nhwc_ld(*dx, "dx"),
+                            N, h, w_, Cin, Cout, cur()), "convT2x2_dgrad");
+  }
+}
+
 bool conv_supported(int64_t cin, int64_t cout) { return b200conv_supported((int)cin, (int)cout) != 0; }
 
 }  // namespace
@@ -291,4 +307,5 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("conv3x3_dgrad(Tensor dy, Tensor w, Tensor(a!) dx) -> ()", &conv3x3_dgrad);
   m.def("conv3x3_wgrad(Tensor x, Tensor dy, Tensor(a!) dw) -> ()", &conv3x3_wgrad);
   m.def("convT2x2_fwd(Tensor x, Tensor w, Tensor bias, Tensor(a!) out) -> ()", &convT2x2_fwd);
+  m.def("convT2x2_bwd(Tensor x, Tensor d_up, Tensor w, Tensor(a!) dw, Tensor(b!)? dx) -> ()", &convT2x2_bwd);
 }

@@ -30,7 +30,8 @@
 #include "umma.cuh"
 #include "../common.cuh"
 #include "b200seg.h"
-#include <mutex>
+#include "tma_host.h"
+#include <cstdlib>
 
 namespace b200 {
 
@@ -48,6 +49,8 @@ struct TapGemmParams {
   int kc_total;                    // channels per tap (K-major B: column stride between taps)
   int n_tiles, block_n, n_total;
   int b_tap_stride;                // MN-major B: column offset between taps
+  int b_row_tap_stride;            // MN-major B: row (K) offset between taps (convT dgrad)
+  int a_mode;                      // 0: 4-D activation box shifted per tap; 1: 5-D 2x2 quadrant gather
   int ocb, groups;                 // output channel box (64/32/16) and groups per N tile
   int out_mode;                    // 0: NHWC store, 1: convT 2x2 scatter
   int convt_cout;
@@ -126,14 +129,16 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
             uint8_t* sb = sa + p.a_bytes;
             mbar_arrive_expect_tx(&bar_full[stage], p.a_bytes + p.b_bytes);
-            tma_load_4d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, w0 + dw, h0 + dh, n0);
+            if (p.a_mode == 0) tma_load_4d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, w0 + dw, h0 + dh, n0);
+            else tma_load_5d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, t & 1, w0, t >> 1, n0 * p.H + h0);
             if (!B_MN) {
               tma_load_2d(sb, &map_b, &bar_full[stage], t * p.kc_total + kc * BLOCK_K, n_tile * p.block_n);
             } else {
               const int nblocks = (p.block_n + 63) >> 6;
               for (int nb = 0; nb < nblocks; ++nb)
                 tma_load_2d(sb + nb * (BLOCK_K * 128), &map_b, &bar_full[stage],
-                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * BLOCK_K);
+                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64,
+                            t * p.b_row_tap_stride + kc * BLOCK_K);
             }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
@@ -157,14 +162,14 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
           const uint32_t sb = sa + p.a_bytes;
+          // descriptors: build once per stage, then only bump the 14-bit address field per K step
+          const uint64_t da0 = make_smem_desc(sa, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+          const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
+                                    : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
 #pragma unroll
-          for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
-            const uint64_t da = make_smem_desc(sa + k4 * 32, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
-            uint64_t db;
-            if (!B_MN) db = make_smem_desc(sb + k4 * 32, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
-            else       db = make_smem_desc(sb + k4 * 2048, BLOCK_K * 128, 1024, LAYOUT_SW128);
-            umma_bf16(d_tmem, da, db, idesc, (it | k4) != 0 ? 1u : 0u);
-          }
+          for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
+            umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc,
+                      (it | k4) != 0 ? 1u : 0u);
           umma_commit(&bar_empty[stage]);                 // frees the smem stage when the MMAs retire
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -321,6 +326,10 @@ struct WgradParams {
   int stages;
   uint32_t a_bytes, b_bytes, stage_bytes;
   float* dw;
+  int convt;                                // 1: dW[(q, co)][ci] of the 2x2 transposed conv
+  int nt_per_q;                             // convT: N tiles per quadrant
+  int H;                                    // convT: low-res height (Y = n*H + y)
+  long long co_stride;                      // floats between consecutive output channels in dw
 };
 
 __global__ void __launch_bounds__(kConvThreads, 1)
@@ -374,10 +383,18 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             int blk = m_tile * 2 + hb;
             if (blk >= p.m_blocks) blk = p.m_blocks - 1;     // padding block: loaded, never stored
             const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
-            tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + (t % 3 - 1), h0 + (t / 3 - 1), n0);
+            const int dw_ = p.convt ? 0 : (t % 3 - 1), dh_ = p.convt ? 0 : (t / 3 - 1);
+            tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0);
           }
-          for (int nb = 0; nb < nblocks; ++nb)
-            tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
+          if (!p.convt) {
+            for (int nb = 0; nb < nblocks; ++nb)
+              tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
+          } else {
+            const int q = n_tile / p.nt_per_q, nt = n_tile % p.nt_per_q;
+            for (int nb = 0; nb < nblocks; ++nb)
+              tma_load_5d(sb + nb * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0, q >> 1,
+                          n0 * p.H + h0);
+          }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -390,13 +407,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
           MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
-          const uint32_t sb = sa + p.a_bytes;
+          const uint64_t da0 = make_smem_desc(sa, 8192, 1024, LAYOUT_SW128);
+          const uint64_t db0 = make_smem_desc(sa + p.a_bytes, 8192, 1024, LAYOUT_SW128);
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t da = make_smem_desc(sa + k4 * 2048, 8192, 1024, LAYOUT_SW128);
-            const uint64_t db = make_smem_desc(sb + k4 * 2048, 8192, 1024, LAYOUT_SW128);
-            umma_bf16(tmem_base, da, db, idesc, (it | k4) != 0 ? 1u : 0u);
-          }
+          for (int k4 = 0; k4 < 4; ++k4)
+            umma_bf16(tmem_base, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc, (it | k4) != 0 ? 1u : 0u);
           umma_commit(&bar_empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -414,8 +429,11 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
       MBAR_WAIT_OR_TRAP(&bar_tfull, 0);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(rb * 32) << 16);
-      float* base = p.dw + (size_t)t * p.Cin + ci;
-      const size_t co_stride = (size_t)9 * p.Cin;
+      float* base = p.dw + (p.convt ? (size_t)0 : (size_t)t * p.Cin) + ci;
+      const size_t co_stride = (size_t)p.co_stride;
+      const int q = p.convt ? n_tile / p.nt_per_q : 0;
+      const int co_base = p.convt ? q * p.Cout + (n_tile % p.nt_per_q) * p.block_n : n_tile * p.block_n;
+      const int co_lim = p.convt ? (q + 1) * p.Cout : p.Cout;
       for (int c0 = 0; c0 < p.block_n; c0 += 32) {
         uint32_t r[32];
         if (p.block_n - c0 >= 32) {
@@ -430,8 +448,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
         if (row_ok) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int co = n_tile * p.block_n + c0 + j;
-            if (c0 + j < p.block_n && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(r[j]));
+            const int co = co_base + c0 + j;
+            if (c0 + j < p.block_n && co < co_lim) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(r[j]));
           }
         }
       }
@@ -444,43 +462,6 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
 
 // =================================================================================================
 // Host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* f = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(f);
-  });
-  return fn;
-}
-
-static CUtensorMapSwizzle swizzle_for_bytes(int inner_bytes) {
-  if (inner_bytes >= 128) return CU_TENSOR_MAP_SWIZZLE_128B;
-  if (inner_bytes >= 64) return CU_TENSOR_MAP_SWIZZLE_64B;
-  return CU_TENSOR_MAP_SWIZZLE_32B;
-}
-
-// rank-R bf16 tensor map; dims[0] is the contiguous one; strides in elements for dims 1..R-1.
-static bool make_map(CUtensorMap* m, const void* base, int rank, const long long* dims, const long long* strides_el,
-                     const int* box, int inner_bytes) {
-  EncodeTiledFn enc = encode_fn();
-  if (!enc) return false;
-  cuuint64_t d[5], s[4];
-  cuuint32_t b[5], e[5];
-  for (int i = 0; i < rank; ++i) { d[i] = (cuuint64_t)dims[i]; b[i] = (cuuint32_t)box[i]; e[i] = 1; }
-  for (int i = 1; i < rank; ++i) s[i - 1] = (cuuint64_t)strides_el[i] * 2;
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, e,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for_bytes(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS;
-}
-
 static int ilog2_floor(int x) { int l = 0; while ((2 << l) <= x) ++l; return l; }
 
 struct TileGeom { int tw_log2, th_log2, tn, tiles_w, tiles_h, tiles_g; };
@@ -525,7 +506,7 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
   return (int)cudaGetLastError();
 }
 
-// mode: 0 fprop, 1 dgrad, 2 convT forward
+// mode: 0 fprop, 1 dgrad, 2 convT forward, 3 convT data gradient
 static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, const float* bias, void* out,
                         long long ld_o, int N, int H, int W, int Kc, int n_total, int conv_cin, float* partials,
                         int* stat_rows_out, bool dry, cudaStream_t st) {
@@ -537,7 +518,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
   p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
   p.H = H; p.W = W; p.N = N;
-  p.taps = (mode == 2) ? 1 : 9;
+  p.taps = (mode == 2) ? 1 : (mode == 3 ? 4 : 9);
   p.flip = (mode == 1) ? -1 : 1;
   p.kc_per_tap = Kc / BK;
   p.kc_total = Kc;
@@ -548,16 +529,18 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.n_tiles = (n_total + p.block_n - 1) / p.block_n;
   p.groups = p.block_n / p.ocb;
   if (p.groups > kMaxGroups || p.block_n % p.ocb) return (int)cudaErrorInvalidValue;
-  p.b_tap_stride = conv_cin;
+  p.b_tap_stride = (mode == 3) ? 0 : conv_cin;
+  p.b_row_tap_stride = (mode == 3) ? Kc : 0;
+  p.a_mode = (mode == 3) ? 1 : 0;
   p.out_mode = (mode == 2) ? 1 : 0;
   p.convt_cout = (mode == 2) ? n_total / 4 : 1;
   if (mode == 2 && (p.convt_cout % p.ocb)) return (int)cudaErrorInvalidValue;
-  if (mode == 2 && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
+  if ((mode == 2 || mode == 3) && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.bias = bias;
   p.partials = partials;
   if (partials != nullptr && (128 % (p.block_n / 8) != 0)) return (int)cudaErrorInvalidValue;
   p.a_bytes = 128 * BK * 2;
-  const bool bmn = (mode == 1);
+  const bool bmn = (mode == 1 || mode == 3);
   const uint32_t b_raw = bmn ? (uint32_t)((p.block_n + 63) / 64) * 64 * BK * 2 : (uint32_t)p.block_n * BK * 2;
   p.b_bytes = b_raw;
   p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
@@ -575,15 +558,24 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
 
   CUtensorMap ma, mb, mo;
   const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
-  {
+  if (mode != 3) {
     long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
     int box[4] = {BK, TW, TH, g.tn};
     if (!make_map(&ma, a, 4, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
+  } else {         // d_up (N, 2H, 2W, C) viewed as (c, dx, x, dy, Y = n*H + y)
+    long long dims[5] = {Kc, 2, W, 2, (long long)N * H};
+    long long str[5] = {1, ld_a, 2 * ld_a, 2 * (long long)W * ld_a, 4 * (long long)W * ld_a};
+    int box[5] = {BK, 1, TW, 1, TH * g.tn};
+    if (!make_map(&ma, a, 5, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
   }
   if (!bmn) {      // weights as [n_total rows][taps*Kc cols], K contiguous
     long long dims[2] = {(long long)p.taps * Kc, n_total}, str[2] = {1, (long long)p.taps * Kc};
     int box[2] = {BK, p.block_n};
     if (!make_map(&mb, w, 2, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
+  } else if (mode == 3) {   // transposed-conv weights [(q, co) rows][ci cols], N = ci contiguous
+    long long dims[2] = {n_total, (long long)4 * Kc}, str[2] = {1, n_total};
+    int box[2] = {64, BK};
+    if (!make_map(&mb, w, 2, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   } else {         // weights as [Kc rows (conv Cout)][9*conv_cin cols], N contiguous
     long long dims[2] = {(long long)9 * conv_cin, Kc}, str[2] = {1, (long long)9 * conv_cin};
     int box[2] = {64, BK};
@@ -639,21 +631,26 @@ extern "C" int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, 
   return run_tap_gemm(2, x, ld_x, w, bias, out, ld_o, N, h, w_, Cin, 4 * Cout, Cin, nullptr, nullptr, false, st);
 }
 
-extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
-                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                     int H, int W, int Cin, int Cout, cudaStream_t st) {
   if (Cin % 8 || Cout % 16) return (int)cudaErrorInvalidValue;
   WgradParams p{};
   TileGeom g = geom_for(N, H, W, 64);
+  if (convt && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
   p.p_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
   p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
   p.Cin = Cin; p.Cout = Cout;
   p.chunks_per_tap = (Cin + 63) / 64;
-  p.m_blocks = 9 * p.chunks_per_tap;
+  p.m_blocks = (convt ? 1 : 9) * p.chunks_per_tap;
   p.m_tiles = (p.m_blocks + 1) / 2;
   p.block_n = Cout <= 256 ? Cout : (Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64));
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
-  p.n_tiles = (Cout + p.block_n - 1) / p.block_n;
+  p.nt_per_q = (Cout + p.block_n - 1) / p.block_n;
+  p.n_tiles = (convt ? 4 : 1) * p.nt_per_q;
+  p.convt = convt;
+  p.H = H;
+  p.co_stride = convt ? Cin : (long long)9 * Cin;
   const int nblocks = (p.block_n + 63) / 64;
   p.a_bytes = 2 * 8192;
   p.b_bytes = nblocks * 8192;
@@ -674,10 +671,15 @@ extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, lon
     int box[4] = {64, TW, TH, g.tn};
     if (!make_map(&mx, x, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   }
-  {
+  if (!convt) {
     long long dims[4] = {Cout, W, H, N}, str[4] = {1, ld_dy, ld_dy * W, ld_dy * W * H};
     int box[4] = {64, TW, TH, g.tn};
     if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  } else {
+    long long dims[5] = {Cout, 2, W, 2, (long long)N * H};
+    long long str[5] = {1, ld_dy, 2 * ld_dy, 2 * (long long)W * ld_dy, 4 * (long long)W * ld_dy};
+    int box[5] = {64, 1, TW, 1, TH * g.tn};
+    if (!make_map(&mdy, dy, 5, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   }
   static bool attr_done = false;
   if (!attr_done) {
@@ -689,4 +691,36 @@ extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, lon
   const size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
   wgrad_kernel<<<base_items * ks, kConvThreads, smem, st>>>(mx, mdy, p);
   return (int)cudaGetLastError();
+}
+
+extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout);
+extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout);
+extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
+                                    int N, int H, int W, int Cin, int Cout, cudaStream_t st);
+
+// Dispatch: halo-strip kernel (wgrad_strip.cu) when the rows are at least 64 pixels wide, else the
+// split-K kernel above.  B200SEG_WGRAD_KERNEL=splitk|strip forces one of them (for benchmarking).
+extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+  static int force = -1;
+  if (force < 0) {
+    const char* e = getenv("B200SEG_WGRAD_KERNEL");
+    force = (e == nullptr) ? 0 : (e[0] == 's' && e[1] == 'p' ? 1 : 2);
+  }
+  const bool strip_ok = (force == 2) ? b200conv_wgrad_strip_supported(N, H, W, Cin, Cout) != 0
+                                     : b200conv_wgrad_strip_preferred(N, H, W, Cin, Cout) != 0;
+  if (strip_ok && force != 1) return b200conv_wgrad_strip(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+  return run_wgrad(0, x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+}
+
+// Backward of ConvTranspose2d(k=2, s=2): d_up is (N, 2h, 2w, Cout) (a channel slice of the concat
+// gradient), x (N, h, w, Cin), w / dw in the kernel layout [(dy, dx, co)][ci].
+extern "C" int b200conv_convT_dgrad(const void* d_up, long long ld_g, const void* w, void* dx, long long ld_dx,
+                                    int N, int h, int w_, int Cin, int Cout, cudaStream_t st) {
+  return run_tap_gemm(3, d_up, ld_g, w, nullptr, dx, ld_dx, N, h, w_, Cout, Cin, Cin, nullptr, nullptr, false, st);
+}
+
+extern "C" int b200conv_convT_wgrad(const void* x, long long ld_x, const void* d_up, long long ld_g, float* dw,
+                                    int N, int h, int w_, int Cin, int Cout, cudaStream_t st) {
+  return run_wgrad(1, x, ld_x, d_up, ld_g, dw, N, h, w_, Cin, Cout, st);
 }

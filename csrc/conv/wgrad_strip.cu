@@ -1,0 +1,225 @@
+// Weight gradient of the 3x3 conv, halo-strip version (W >= 64):
+//     dW[co][(r,s)][ci] += sum_p dy[p][co] * x[p + (r-1, s-1)][ci]                 
+//
+// The plain split-K kernel in conv_tc.cu re-reads the input once per filter tap (9x) from L2 and is
+// bandwidth-bound for the wide, shallow layers that dominate the U-Net.  Here one CTA owns ONE
+// 64-channel chunk of Cin and ONE 64-channel tile of Cout and marches down image columns:
+//
+//   * a K step is 64 consecutive pixels of one image row.  The producer loads ONE new input "strip"
+//     per step -- 66 pixels (one halo pixel each side) x 64 channels, 128-byte swizzled -- and the
+//     matching 64 x 64 dy tile.  The three strips of rows h-1, h, h+1 live in a ring, so every input
+//     byte is fetched once per (Cin chunk, Cout tile) instead of nine times.
+//   * all nine taps are UMMA operands that point INTO those strips: tap (r,s) is the window of 64
+//     pixel-rows starting s rows into strip r.  tcgen05 applies the 128-byte swizzle as a function
+//     of the absolute shared-memory address, so a window that starts on any 128-byte row is a valid
+//     MN-major operand (probed on hardware, csrc/standalone_umma_probe.cu exp 5).  Two taps of the
+//     same strip form one M = 128 tile (leading byte offset = one row = 128 B); per filter row that
+//     is {(r,0),(r,1)} and {(r,2), unused}: six accumulators of 64 columns in TMEM (384 of 512).
+//   * the accumulators persist across all the pixels the CTA visits; the epilogue runs once and adds
+//     the 9 x 64 x 64 block into the fp32 gradient buffer with red.global.add (the buffer accumulates
+//     over micro-batches anyway, R:756).
+// Out-of-image strips (row -1, row H, the halo columns) are zero-filled by TMA = the conv padding.
+#include "umma.cuh"
+#include "../common.cuh"
+#include "b200seg.h"
+#include "tma_host.h"
+
+namespace b200 {
+
+constexpr int kWsThreads = 192;
+constexpr int kWsStages = 8;
+constexpr uint32_t kStripBytes = 9216;       // 66 rows x 128 B = 8448, padded to 9 KiB (72 rows)
+constexpr uint32_t kDyBytes = 8192;          // 64 pixels x 64 channels
+constexpr uint32_t kWsStageBytes = kStripBytes + kDyBytes;
+
+struct WgradStripParams {
+  int N, H, W, Cin, Cout;
+  int chunks, n_tiles, groups;         // Cin/64 (rounded up), Cout/64 (rounded up), chunks * n_tiles
+  int ctas_per_group;
+  int wsegs, rows_per_piece, pieces_per_col, pieces;   // pieces per group
+  float* dw;
+};
+
+__global__ void __launch_bounds__(kWsThreads, 1)
+wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
+                   const WgradStripParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t bar_full[kWsStages], bar_empty[kWsStages];
+  __shared__ __align__(8) uint64_t bar_done;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  const int group = blockIdx.x % p.groups;
+  const int member = blockIdx.x / p.groups;              // which CTA of the group
+  const int chunk = group % p.chunks;
+  const int n_tile = group / p.chunks;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_dy);
+    for (int s = 0; s < kWsStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    mbar_init(&bar_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(&tmem_base_s);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  const bool has_work = member < p.pieces;
+
+  if (warp == 0) {
+    // ------------------------------------------------ producer ------------------------------------
+    if (elect_one() && has_work) {
+      uint32_t q = 0;                                      // global stage counter
+      for (int piece = member; piece < p.pieces; piece += p.ctas_per_group) {
+        const int col = piece / p.pieces_per_col, seg = piece % p.pieces_per_col;
+        const int n = col / p.wsegs, w0 = (col % p.wsegs) * 64;
+        const int h0 = seg * p.rows_per_piece;
+        const int h1 = min(p.H, h0 + p.rows_per_piece);
+        // stage j of the piece carries input row (h0 - 1 + j); from j = 2 on it also carries the dy
+        // tile of output row (h0 + j - 2).
+        const int nst = (h1 - h0) + 2;
+        for (int j = 0; j < nst; ++j, ++q) {
+          const int st = q % kWsStages;
+          MBAR_WAIT_OR_TRAP(&bar_empty[st], ((q / kWsStages) & 1) ^ 1);
+          uint8_t* sx = smem + (size_t)st * kWsStageBytes;
+          const bool with_dy = j >= 2;
+          mbar_arrive_expect_tx(&bar_full[st], 66 * 128 + (with_dy ? kDyBytes : 0));
+          tma_load_4d(sx, &map_x, &bar_full[st], chunk * 64, w0 - 1, h0 - 1 + j, n);
+          if (with_dy) tma_load_4d(sx + kStripBytes, &map_dy, &bar_full[st], n_tile * 64, w0, h0 + j - 2, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer ----------------------------------
+    if (elect_one() && has_work) {
+      const uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+      uint32_t q = 0;
+      bool first = true;
+      for (int piece = member; piece < p.pieces; piece += p.ctas_per_group) {
+        const int seg = piece % p.pieces_per_col;
+        const int h0 = seg * p.rows_per_piece;
+        const int h1 = min(p.H, h0 + p.rows_per_piece);
+        const int nst = (h1 - h0) + 2;
+        for (int j = 0; j < nst; ++j, ++q) {
+          const int st = q % kWsStages;
+          MBAR_WAIT_OR_TRAP(&bar_full[st], (q / kWsStages) & 1);
+          if (j < 2) continue;                              // halo rows of the piece: loaded only
+          tc_fence_after();
+          // descriptors: build once per operand base, then only bump the 14-bit address field
+          const uint64_t db0 = make_smem_desc(smem_u32(smem + (size_t)st * kWsStageBytes + kStripBytes), 8192, 1024,
+                                              LAYOUT_SW128);
+          const uint32_t acc0 = first ? 0u : 1u;
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const uint64_t da0 = make_smem_desc(
+                smem_u32(smem + (size_t)((q - 2 + r) % kWsStages) * kWsStageBytes), 128, 1024, LAYOUT_SW128);
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {          // {(r,0),(r,1)} and {(r,2), unused}
+              const uint32_t d_tmem = tmem_base + (r * 2 + half) * 64;
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                umma_bf16(d_tmem, da0 + ((half * 256 + k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
+                          k4 == 0 ? acc0 : 1u);
+            }
+          }
+          first = false;
+          umma_commit(&bar_empty[(q - 2) % kWsStages]);    // oldest strip is no longer needed
+          if (j == nst - 1) {                               // end of the piece: free the other two
+            umma_commit(&bar_empty[(q - 1) % kWsStages]);
+            umma_commit(&bar_empty[st]);
+          }
+        }
+      }
+      umma_commit(&bar_done);
+    }
+  } else if (has_work) {
+    // ------------------------------------------------ epilogue (once) -----------------------------
+    const int rb = warp & 3;
+    const int row = rb * 32 + lane;                         // accumulator row: tap half + channel
+    const int ci = chunk * 64 + (row & 63);
+    MBAR_WAIT_OR_TRAP(&bar_done, 0);
+    tc_fence_after();
+    const size_t co_stride = (size_t)9 * p.Cin;
+#pragma unroll 1
+    for (int acc = 0; acc < 6; ++acc) {
+      const int r = acc >> 1, half = acc & 1;
+      const int s = half * 2 + (row >> 6);                  // tap column: 0,1 | 2,(3 = unused)
+      if (s > 2) continue;                                  // warp-uniform (row >> 6 is per warp pair)
+      const bool row_ok = ci < p.Cin;
+      float* base = p.dw + (size_t)(r * 3 + s) * p.Cin + ci;
+      const uint32_t t_addr = tmem_base + acc * 64 + (static_cast<uint32_t>(rb * 32) << 16);
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(t_addr + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int co = n_tile * 64 + c0 + j;
+          if (row_ok && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(v[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Supported whenever a row holds at least one 64-pixel strip.  `preferred` additionally encodes the
+// measured crossover: with 64-column accumulators the UMMA is shared-memory-bound (67 % of peak) and
+// one tile in four is padding, so for Cout > 128 (layers that are not L2-bound anyway) the split-K
+// kernel with 256-column tiles is faster (profiles/conv_layers_*.txt).
+extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout) {
+  (void)N; (void)H;
+  return (W >= 64 && Cin % 8 == 0 && Cout % 8 == 0) ? 1 : 0;
+}
+extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout) {
+  return (b200conv_wgrad_strip_supported(N, H, W, Cin, Cout) && Cout <= 128) ? 1 : 0;
+}
+
+extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
+                                    int N, int H, int W, int Cin, int Cout, cudaStream_t st) {
+  if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return (int)cudaErrorInvalidValue;
+  WgradStripParams p{};
+  p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
+  p.chunks = (Cin + 63) / 64;
+  p.n_tiles = (Cout + 63) / 64;
+  p.groups = p.chunks * p.n_tiles;
+  p.wsegs = (W + 63) / 64;
+  p.rows_per_piece = H < 32 ? H : 32;
+  p.pieces_per_col = (H + p.rows_per_piece - 1) / p.rows_per_piece;
+  p.pieces = N * p.wsegs * p.pieces_per_col;
+  int cpg = kNumSMs / p.groups;
+  if (cpg < 1) cpg = 1;
+  if (cpg > p.pieces) cpg = p.pieces;
+  p.ctas_per_group = cpg;
+  p.dw = dw;
+  CUtensorMap mx, mdy;
+  {
+    long long dims[4] = {Cin, W, H, N}, str[4] = {1, ld_x, ld_x * W, ld_x * W * H};
+    int box[4] = {64, 66, 1, 1};
+    if (!make_map(&mx, x, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  }
+  {
+    long long dims[4] = {Cout, W, H, N}, str[4] = {1, ld_dy, ld_dy * W, ld_dy * W * H};
+    int box[4] = {64, 64, 1, 1};
+    if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  }
+  static bool attr_done = false;
+  const size_t smem = (size_t)kWsStages * kWsStageBytes + 1024;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  wgrad_strip_kernel<<<p.groups * cpg, kWsThreads, smem, st>>>(mx, mdy, p);
+  return (int)cudaGetLastError();
+}

@@ -17,6 +17,9 @@ namespace b200 {
 constexpr int kHeadThreads = 256;
 constexpr int kHeadWarps = kHeadThreads / 32;
 
+// Per warp: a tile of 32 pixels staged through shared memory so that every global access is a
+// coalesced 16-byte vector (lane = chunk), the per-pixel math runs lane = pixel, and the dW
+// accumulation runs lane = channel pair.
 template <int KMAX>
 __global__ void __launch_bounds__(kHeadThreads)
 head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float* __restrict__ w,
@@ -24,22 +27,27 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
                int K, float grad_scale, __nv_bfloat16* __restrict__ da, long long ld_da,
                float* __restrict__ dw, float* __restrict__ db, uint8_t* __restrict__ pred,
                float* __restrict__ loss_acc, float* __restrict__ workspace,
-               unsigned int* __restrict__ counter) {
-  extern __shared__ float sm[];
-  float* s_w = sm;                                  // [K][C]
-  float* s_b = s_w + K * C;                         // [K]
-  float* s_dl = s_b + KMAX;                         // [warps][32][KMAX]
-  float* s_red = s_dl + kHeadWarps * 32 * KMAX;     // [K*C + K + 2] block reduction
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+               unsigned int* __restrict__ counter, int warps) {
+  extern __shared__ __align__(16) uint8_t smraw[];
+  const int pitch = C + 8;                                    // bf16 elements per tile row
   const int nred = K * C + K + 2;
-  for (int i = threadIdx.x; i < K * C; i += kHeadThreads) s_w[i] = w[i];
-  for (int i = threadIdx.x; i < K; i += kHeadThreads) s_b[i] = bias[i];
-  for (int i = threadIdx.x; i < nred; i += kHeadThreads) s_red[i] = 0.f;
+  float* s_w = reinterpret_cast<float*>(smraw);              // [K][C]
+  float* s_b = s_w + K * C;                                   // [KMAX]
+  float* s_red = s_b + KMAX;                                  // [nred]
+  float* s_dl = s_red + ((nred + 3) & ~3);                    // [warps][32][KMAX]
+  __nv_bfloat16* s_tiles = reinterpret_cast<__nv_bfloat16*>(s_dl + warps * 32 * KMAX);   // [warps][2][32][pitch]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < K * C; i += blockDim.x) s_w[i] = w[i];
+  for (int i = threadIdx.x; i < K; i += blockDim.x) s_b[i] = bias[i];
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) s_red[i] = 0.f;
   __syncthreads();
 
   const bool bwd = (da != nullptr);
   const int CV = C >> 3;
-  const int cpl = (C + 31) / 32;                    // channels per lane in the dW phase (<= 8)
+  const int NP = (C + 63) >> 6;                               // bf16 pairs per lane in the dW phase (<= 4)
+  __nv_bfloat16* t_a = s_tiles + (size_t)warp * 2 * 32 * pitch;
+  __nv_bfloat16* t_da = t_a + 32 * pitch;
+  float* my_dl = s_dl + warp * 32 * KMAX;
   float accw[KMAX][8];
   float accb[KMAX];
 #pragma unroll
@@ -49,27 +57,36 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
     for (int j = 0; j < 8; ++j) accw[k][j] = 0.f;
   }
   float loss_local = 0.f, correct_local = 0.f;
-  float* my_dl = s_dl + warp * 32 * KMAX;
 
   const long long chunks = (P + 31) / 32;
-  for (long long ch = (long long)blockIdx.x * kHeadWarps + warp; ch < chunks;
-       ch += (long long)gridDim.x * kHeadWarps) {
-    const long long p = ch * 32 + lane;
+  for (long long ch = (long long)blockIdx.x * warps + warp; ch < chunks; ch += (long long)gridDim.x * warps) {
+    const long long p0 = ch * 32;
+    // 1. coalesced tile load
+    for (int i = lane; i < 32 * CV; i += 32) {
+      const int px = i / CV, cv = i - px * CV;
+      bf16x8 v;
+      if (p0 + px < P) v = ld8(a + (p0 + px) * ld_a + cv * 8);
+      else { v.v[0] = v.v[1] = v.v[2] = v.v[3] = __floats2bfloat162_rn(0.f, 0.f); }
+      *reinterpret_cast<bf16x8*>(t_a + px * pitch + cv * 8) = v;
+    }
+    __syncwarp();
+    // 2. logits, softmax, loss (lane = pixel)
+    const long long p = p0 + lane;
     const bool valid = p < P;
     float z[KMAX];
 #pragma unroll
     for (int k = 0; k < KMAX; ++k) z[k] = (k < K) ? s_b[k] : -INFINITY;
-    if (valid) {
-      for (int cv = 0; cv < CV; ++cv) {
-        float f[8];
-        unpack8(ld8(a + p * ld_a + cv * 8), f);
+    for (int cv = 0; cv < CV; ++cv) {
+      float f[8];
+      unpack8(*reinterpret_cast<const bf16x8*>(t_a + lane * pitch + cv * 8), f);
 #pragma unroll
-        for (int k = 0; k < KMAX; ++k)
-          if (k < K) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) z[k] = fmaf(f[j], s_w[k * C + cv * 8 + j], z[k]);
-          }
-      }
+      for (int k = 0; k < KMAX; ++k)
+        if (k < K) {
+          const float4 w0 = *reinterpret_cast<const float4*>(s_w + k * C + cv * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(s_w + k * C + cv * 8 + 4);
+          z[k] = fmaf(f[0], w0.x, fmaf(f[1], w0.y, fmaf(f[2], w0.z, fmaf(f[3], w0.w, z[k]))));
+          z[k] = fmaf(f[4], w1.x, fmaf(f[5], w1.y, fmaf(f[6], w1.z, fmaf(f[7], w1.w, z[k]))));
+        }
     }
     float mx = z[0];
     int arg = 0;
@@ -97,30 +114,40 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
         my_dl[lane * KMAX + k] = dl[k];
         accb[k] += dl[k];
       }
-      if (valid) {
-        for (int cv = 0; cv < CV; ++cv) {
-          float o[8];
+      // 3. da row -> smem tile
+      for (int cv = 0; cv < CV; ++cv) {
+        float o[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] = 0.f;
+        for (int j = 0; j < 8; ++j) o[j] = 0.f;
 #pragma unroll
-          for (int k = 0; k < KMAX; ++k)
-            if (k < K) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) o[j] = fmaf(dl[k], s_w[k * C + cv * 8 + j], o[j]);
-            }
-          st8(da + p * ld_da + cv * 8, pack8(o));
-        }
+        for (int k = 0; k < KMAX; ++k)
+          if (k < K) {
+            const float4 w0 = *reinterpret_cast<const float4*>(s_w + k * C + cv * 8);
+            const float4 w1 = *reinterpret_cast<const float4*>(s_w + k * C + cv * 8 + 4);
+            o[0] = fmaf(dl[k], w0.x, o[0]); o[1] = fmaf(dl[k], w0.y, o[1]);
+            o[2] = fmaf(dl[k], w0.z, o[2]); o[3] = fmaf(dl[k], w0.w, o[3]);
+            o[4] = fmaf(dl[k], w1.x, o[4]); o[5] = fmaf(dl[k], w1.y, o[5]);
+            o[6] = fmaf(dl[k], w1.z, o[6]); o[7] = fmaf(dl[k], w1.w, o[7]);
+          }
+        *reinterpret_cast<bf16x8*>(t_da + lane * pitch + cv * 8) = pack8(o);
       }
       __syncwarp();
-      // dW phase: lane owns channels lane, lane+32, ...; walks the 32 pixels of this chunk.
-      const long long p0 = ch * 32;
-      const int npx = (int)((P - p0) < 32 ? (P - p0) : 32);
-      for (int i = 0; i < npx; ++i) {
+      // 4. coalesced tile store
+      for (int i = lane; i < 32 * CV; i += 32) {
+        const int px = i / CV, cv = i - px * CV;
+        if (p0 + px < P) st8(da + (p0 + px) * ld_da + cv * 8, *reinterpret_cast<const bf16x8*>(t_da + px * pitch + cv * 8));
+      }
+      // 5. dW: lane owns channel pairs (2*lane + 64*j); walks the 32 pixels of the tile
+#pragma unroll 4
+      for (int i = 0; i < 32; ++i) {
         float av[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int c = lane + 32 * j;
-          av[j] = (j < cpl && c < C) ? __bfloat162float(a[(p0 + i) * ld_a + c]) : 0.f;
+        for (int j = 0; j < 4; ++j) {
+          const int c = j * 64 + lane * 2;
+          float2 t = make_float2(0.f, 0.f);
+          if (j < NP && c < C) t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(t_a + i * pitch + c));
+          av[2 * j] = t.x;
+          av[2 * j + 1] = t.y;
         }
 #pragma unroll
         for (int k = 0; k < KMAX; ++k) {
@@ -129,24 +156,24 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
           for (int j = 0; j < 8; ++j) accw[k][j] = fmaf(d, av[j], accw[k][j]);
         }
       }
-      __syncwarp();
     }
+    __syncwarp();
   }
   // ---- block reduction -> per-CTA partial ----------------------------------------------------
   loss_local = warp_sum(loss_local);
   correct_local = warp_sum(correct_local);
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) accb[k] = warp_sum(accb[k]);
-  for (int wv = 0; wv < kHeadWarps; ++wv) {          // fixed warp order: deterministic sums
+  for (int wv = 0; wv < warps; ++wv) {               // fixed warp order: deterministic sums
     if (warp == wv) {
       if (bwd) {
 #pragma unroll
         for (int k = 0; k < KMAX; ++k)
           if (k < K) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int c = lane + 32 * j;
-              if (j < cpl && c < C) s_red[k * C + c] += accw[k][j];
+            for (int j = 0; j < 4; ++j) {
+              const int c = j * 64 + lane * 2;
+              if (j < NP && c < C) { s_red[k * C + c] += accw[k][2 * j]; s_red[k * C + c + 1] += accw[k][2 * j + 1]; }
             }
             if (lane == 0) s_red[K * C + k] += accb[k];
           }
@@ -158,9 +185,8 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
     }
     __syncthreads();
   }
-  __syncthreads();
   float* mine = workspace + (size_t)blockIdx.x * nred;
-  for (int i = threadIdx.x; i < nred; i += kHeadThreads) mine[i] = s_red[i];
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) mine[i] = s_red[i];
   __threadfence();
   __shared__ unsigned int s_last;
   __syncthreads();
@@ -168,7 +194,7 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  for (int i = threadIdx.x; i < nred; i += kHeadThreads) {
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) {
     float t = 0.f;
     for (unsigned int b = 0; b < gridDim.x; ++b) t += workspace[(size_t)b * nred + i];
     if (i < K * C) { if (bwd) dw[i] += t; }
@@ -194,23 +220,30 @@ extern "C" int b200seg_head_ce(const void* a, long long ld_a, const float* w, co
                                float* loss_acc, void* workspace, cudaStream_t st) {
   if (C % 8 || C > 256 || K < 1 || K > 16) return (int)cudaErrorInvalidValue;
   const int KMAX = K <= 8 ? 8 : 16;
+  const int warps = C <= 128 ? 8 : 4;
+  const int threads = warps * 32;
   long long chunks = (P + 31) / 32;
-  int grid = (int)((chunks + kHeadWarps - 1) / kHeadWarps);
+  int grid = (int)((chunks + warps - 1) / warps);
   if (grid > 2 * kNumSMs) grid = 2 * kNumSMs;
   if (grid < 1) grid = 1;
   const int nred = K * C + K + 2;
-  size_t smem = sizeof(float) * ((size_t)K * C + KMAX + (size_t)kHeadWarps * 32 * KMAX + nred);
+  size_t smem = sizeof(float) * ((size_t)K * C + KMAX + ((nred + 3) & ~3) + (size_t)warps * 32 * KMAX) +
+                (size_t)warps * 2 * 32 * (C + 8) * 2;
   float* ws = (float*)workspace;
   unsigned int* counter = (unsigned int*)((char*)workspace + b200seg_head_ce_workspace_bytes(C, K) - 256);
+  cudaError_t e;
   if (KMAX == 8) {
-    head_ce_kernel<8><<<grid, kHeadThreads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
-                                                        grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred,
-                                                        loss_acc, ws, counter);
+    e = cudaFuncSetAttribute(head_ce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    head_ce_kernel<8><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
+                                                   grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc,
+                                                   ws, counter, warps);
   } else {
-    cudaFuncSetAttribute(head_ce_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    head_ce_kernel<16><<<grid, kHeadThreads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
-                                                         grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred,
-                                                         loss_acc, ws, counter);
+    e = cudaFuncSetAttribute(head_ce_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    head_ce_kernel<16><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
+                                                    grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc,
+                                                    ws, counter, warps);
   }
   return (int)cudaGetLastError();
 }

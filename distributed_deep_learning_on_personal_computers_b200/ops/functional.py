@@ -168,12 +168,20 @@ def convT2x2_fwd(x, w_param, w_lp, bias, out, impl=None):
     ref.convT2x2_fwd(x, w_param, bias, out)
 
 
-def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx):
-    """Backward of the transposed conv.  Data gradient = a stride-2 2x2 conv of d_up; weight
-    gradient = that conv's weight gradient.  (Library call for now: ~3% of the step's FLOPs.)"""
+def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx, impl=None):
+    """Backward of the transposed conv.  Data gradient = a stride-2 2x2 conv of d_up (a tap GEMM over
+    the four quadrants, gathered by a 5-D TMA box); weight gradient = the wgrad kernel with the
+    quadrant as the N tile.  ``dw_param`` is the logical (Cin,Cout,2,2) view of the flat gradient."""
     if _native(x):
         cout4, cin = w_lp.shape
         cout = cout4 // 4
+        if _use_tc(cin, cout, impl):
+            part = torch.empty(_ops().stats_rows(), 2, cout, dtype=torch.float32, device=x.device)
+            _ops().channel_stats(d_up, part)
+            dbias.add_(part[:, 0, :].sum(0))
+            _ops().convT2x2_bwd(x, d_up, w_lp, _flat_of(dw_param).reshape(4 * cout, cin), dx)
+            _tick(3)
+            return
         wl = w_lp.view(2, 2, cout, cin).permute(3, 2, 0, 1)               # logical (Cin,Cout,2,2)
         g = d_up.permute(0, 3, 1, 2)
         dbias.add_(g.sum(dim=(0, 2, 3), dtype=torch.float32))

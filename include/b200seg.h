@@ -92,6 +92,11 @@ int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_d
                    int H, int W, int Cin, int Cout, cudaStream_t st);
 int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, const float* bias, void* out,
                        long long ld_o, int N, int h, int w_, int Cin, int Cout, cudaStream_t st);
+/* backward of the transposed conv: d_up (N,2h,2w,Cout) slice; w, dw laid out [(dy,dx,co)][ci] */
+int b200conv_convT_dgrad(const void* d_up, long long ld_g, const void* w, void* dx, long long ld_dx, int N,
+                         int h, int w_, int Cin, int Cout, cudaStream_t st);
+int b200conv_convT_wgrad(const void* x, long long ld_x, const void* d_up, long long ld_g, float* dw, int N,
+                         int h, int w_, int Cin, int Cout, cudaStream_t st);
 
 #ifdef __cplusplus
 }

@@ -83,3 +83,27 @@ def test_convT2x2_fwd_into_concat_slice(N, h, w, C):
                               bias, stride=2).permute(0, 2, 3, 1)
     torch.testing.assert_close(cat[..., :C].float(), want, rtol=2e-2, atol=2e-2)
     assert (cat[..., C:] == 0).all()
+
+
+@pytest.mark.parametrize("N,h,w,C", [(2, 16, 16, 64), (1, 8, 8, 256), (2, 32, 32, 128), (4, 4, 4, 64)])
+def test_convT2x2_bwd(N, h, w, C):
+    torch.manual_seed(8)
+    x = torch.randn(N, h, w, C, device=DEV).to(torch.bfloat16)
+    wp = torch.randn(C, C, 2, 2, device=DEV) * 0.05
+    w_lp = wp.permute(2, 3, 1, 0).contiguous().view(4 * C, C).to(torch.bfloat16)
+    dcat = (torch.randn(N, 2 * h, 2 * w, C + 64, device=DEV) * 0.1).to(torch.bfloat16)
+    d_up = dcat[..., :C]                                   # gradient arrives as a concat-buffer slice
+    flat = torch.ones(4 * C * C, device=DEV)
+    dw_param = flat.view(2, 2, C, C).permute(3, 2, 0, 1)     # logical (Cin, Cout, 2, 2) view
+    dbias = torch.zeros(C, device=DEV)
+    dx = torch.empty(N, h, w, C, dtype=torch.bfloat16, device=DEV)
+    Fn.convT2x2_bwd(x, d_up, wp, w_lp, dw_param, dbias, dx, impl="tcgen05")
+    wl = w_lp.float().view(2, 2, C, C).permute(3, 2, 0, 1)
+    dw_ref = torch.ones(C, C, 2, 2, device=DEV)
+    db_ref = torch.zeros(C, device=DEV)
+    dx_ref = torch.empty(N, h, w, C, device=DEV)
+    ref.convT2x2_bwd(x.float(), d_up.float(), wl, dw_ref, db_ref, dx_ref)
+    torch.testing.assert_close(dx.float(), dx_ref, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(dbias, db_ref, rtol=1e-3, atol=1e-2)
+    scale = (dw_ref - 1).abs().max().item()
+    assert (dw_param - dw_ref).abs().max().item() <= 1e-2 * scale + 1e-3
