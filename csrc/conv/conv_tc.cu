@@ -56,6 +56,7 @@ struct TapGemmParams {
   int convt_cout;
   int stages;
   uint32_t a_bytes, b_bytes, stage_bytes, staging_bytes;
+  int staging_bufs;                // 1 or 2 output staging tiles (2: TMA store of tile i overlaps tile i+1)
   const float* bias;
   float* partials;
 };
@@ -201,7 +202,11 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const bool has_bias = p.bias != nullptr;
     int acc = 0;
     uint32_t acc_phase = 0;
+    int sbuf = 0;
+    uint8_t* const staging0 = staging;
     for (int m = m_first; m < p.m_tiles; m += m_step) {
+      uint8_t* const staging = staging0 + (size_t)sbuf * p.staging_bytes;     // this tile's staging buffer
+      if (p.staging_bufs == 2) sbuf ^= 1;
       const int twi = m % p.tiles_w;
       const int thi = (m / p.tiles_w) % p.tiles_h;
       const int g_img = m / (p.tiles_w * p.tiles_h);
@@ -277,13 +282,16 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           }
         }
         tma_store_commit();
-        tma_store_wait_read<0>();                          // staging may be overwritten again
+        // the buffer written NEXT must be free: with two buffers that is the store issued one tile ago
+        if (p.staging_bufs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
       }
       named_bar_sync(1, 128);
     }
     if (p.partials != nullptr) {
       // combine the (128 / cpr) threads that share a chunk column, then one row of partials per CTA
-      float* red = reinterpret_cast<float*>(staging);    // [128/cpr][2][block_n]
+      if (et == 0) tma_store_wait_read<0>();
+      named_bar_sync(1, 128);
+      float* red = reinterpret_cast<float*>(staging0);   // [128/cpr][2][block_n]
       const int ncol = p.block_n;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -546,7 +554,8 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
   p.staging_bytes = 128u * p.block_n * 2;
   if (p.staging_bytes < 8192) p.staging_bytes = 8192;
-  int stages = (int)((kSmemBudget - p.staging_bytes) / p.stage_bytes);
+  p.staging_bufs = (2 * p.staging_bytes + 4 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
+  int stages = (int)((kSmemBudget - p.staging_bufs * p.staging_bytes) / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return (int)cudaErrorInvalidValue;
   p.stages = stages;
@@ -591,7 +600,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     int box[5] = {p.ocb, 1, TW, 1, TH * g.tn};
     if (!make_map(&mo, out, 5, dims, str, box, p.ocb * 2)) return (int)cudaErrorInvalidValue;
   }
-  const size_t smem = (size_t)p.stages * p.stage_bytes + p.staging_bytes + 1024;
+  const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.staging_bufs * p.staging_bytes + 1024;
   if (bmn) {
     if (BK == 64) return launch_tap<64, true>(ma, mb, mo, p, grid, smem, st);
     if (BK == 32) return launch_tap<32, true>(ma, mb, mo, p, grid, smem, st);

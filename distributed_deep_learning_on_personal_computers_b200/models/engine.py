@@ -72,6 +72,15 @@ class NativeEngine:
         self._buffers = dict(model.named_buffers())
         self._build()
         self.training = True
+        # The stem reads 3 real + 13 zero channels (one UMMA K step).  Its bf16 weights are kept
+        # zero-padded to (Cout, 3, 3, IN_PAD) next to the flat buffer, refreshed every forward, and its
+        # weight gradient is produced padded and folded back into the flat gradient.
+        self.stem = "down_conv1.double_conv.double_conv.0"
+        cout = self._params[self.stem + ".weight"].shape[0]
+        self.stem_pad = self.on_gpu and model.in_channels < IN_PAD
+        if self.stem_pad:
+            self.stem_w = torch.zeros(cout, 3, 3, IN_PAD, dtype=self.act_dtype, device=self.device)
+            self.stem_dw = torch.zeros(cout, 3, 3, IN_PAD, dtype=torch.float32, device=self.device)
 
     # -- helpers -------------------------------------------------------------------------------
     def _new(self, *shape, dtype=None):
@@ -168,6 +177,9 @@ class NativeEngine:
     def _stage_fwd(self, st: _Stage) -> None:
         sp = st.spec
         w = self._w3(self.flat_lp, sp.name + ".weight")
+        if self.stem_pad and sp.name == self.stem:
+            self.stem_w[..., :w.shape[3]].copy_(w)
+            w = self.stem_w
         bias = self._seg(self.flat_p, sp.name + ".bias")
         # the conv bias is NOT added by the conv: BatchNorm absorbs it (see ops.reference.bn_finalize)
         st.stats = Fn.conv3x3_fwd(st.x, w, None, st.y, want_stats=self.training,
@@ -188,8 +200,13 @@ class NativeEngine:
                             self._seg(self.flat_g, bn + ".weight"),
                             self._seg(self.flat_g, bn + ".bias"),
                             self._seg(self.flat_g, sp.name + ".bias"), st.dy)
-        Fn.conv3x3_wgrad(st.x, st.dy, self._w3(self.flat_g, sp.name + ".weight"),
-                         impl=self.conv_impl)
+        dw = self._w3(self.flat_g, sp.name + ".weight")
+        if self.stem_pad and sp.name == self.stem:
+            self.stem_dw.zero_()
+            Fn.conv3x3_wgrad(st.x, st.dy, self.stem_dw, impl=self.conv_impl)
+            dw.add_(self.stem_dw[..., :dw.shape[3]])
+        else:
+            Fn.conv3x3_wgrad(st.x, st.dy, dw, impl=self.conv_impl)
         if need_dx and st.dx is not None:
             Fn.conv3x3_dgrad(st.dy, self._w3(self.flat_lp, sp.name + ".weight"), st.dx,
                              impl=self.conv_impl)

@@ -48,6 +48,9 @@ def available(ctx: DistContext) -> bool:
 class SymmetricAllReduce:
     def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None):
         import torch.distributed._symmetric_memory as symm_mem
+        from ..ops import loader
+        if loader.library() is None:
+            raise RuntimeError(f"native all-reduce needs the b200seg library: {loader.load_error()}")
         self.ctx, self.codec = ctx, codec
         self.group = group or dist.group.WORLD
         dev = like_flat.device

@@ -1,0 +1,113 @@
+"""Multi-GPU: the peer-memory all-reduce kernels against NCCL, and a 2-rank training run.
+
+Launched as one process per GPU by the test itself (torch.multiprocessing), NCCL for the handle
+exchange, 127.0.0.1 rendezvous.  Needs >= 2 GPUs; skipped otherwise.
+"""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _ar_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    from distributed_deep_learning_on_personal_computers_b200.parallel import symm, dist as pdist
+    from distributed_deep_learning_on_personal_computers_b200.parallel.codecs import get_codec
+    ctx = pdist.DistContext(rank, world, rank, torch.device("cuda", rank), "nccl", False)
+    out = {"available": symm.available(ctx)}
+    if out["available"]:
+        for codec, n in (("fp32", 1 << 16), ("fp32", 5_000_000), ("bf16", 1_000_003), ("q201", 700_001),
+                         ("int8s", 333_333), ("fp8", 100_000)):
+            g = torch.Generator(device="cuda").manual_seed(100 + rank)
+            x = torch.randn(n, device="cuda", generator=g) * 0.01
+            ar = symm.SymmetricAllReduce(x, ctx, get_codec(codec))
+            for rep in range(3):                         # epochs advance; buffer is reused in place
+                ar.buffer.copy_(x)
+                ar.all_reduce_()
+                got = ar.buffer.clone()
+                c = get_codec(codec)
+                q_, s_ = c.encode(x)
+                ref = c.decode(q_, s_)
+                dist.all_reduce(ref)
+                err = (got - ref).abs().max().item()
+                tol = 0.0 if codec == "fp32" and world == 2 else 1e-6 + 1e-5 * ref.abs().max().item()
+                # bit-identical across ranks (reference guarantee R:402-433)
+                chk = got.double().sum().reshape(1)
+                lst = [torch.zeros_like(chk) for _ in range(world)]
+                dist.all_gather(lst, chk)
+                same = all(torch.equal(lst[0], t) for t in lst)
+                out[f"{codec}:{n}:{rep}"] = (err, tol, same)
+    dist.barrier(device_ids=[rank])
+    if rank == 0:
+        q.put(out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_native_allreduce_matches_nccl():
+    world = min(torch.cuda.device_count(), 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ar_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=150)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res.pop("available"), "symmetric memory path not available on this box"
+    for k, (err, tol, same) in res.items():
+        assert err <= tol, (k, err, tol)
+        assert same, k
+
+
+def _train_worker(rank, world, port, comm, q, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
+    from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    cfg = TrainConfig(base_channels=32, tile=64, train_tiles=32, holdout_tiles=0, batch_size=4, sync_every=2,
+                      epochs=2, codec="fp32", comm=comm, device="cuda", out_dir=out_dir, sample_images=0,
+                      lr=2e-3, timeout_s=120).apply_env()
+    tr = Trainer(cfg)
+    losses = []
+    for _ in range(3):
+        losses.append(tr.train_epoch()["mean_loss"])
+        tr.epoch += 1
+    q.put((rank, tr.sync.backend, losses, tr.model.flat["param"].double().sum().item()))
+    tr.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("comm", ["native", "torch"])
+def test_two_rank_training_replicas_identical(comm, tmp_path):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_train_worker, args=(r, world, port, comm, q, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=150) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, b0, l0, d0), (_, b1, l1, d1) = res
+    assert b0 == b1 == comm
+    assert d0 == d1                                  # bit-identical replicas
+    assert l0[-1] < l0[0]
