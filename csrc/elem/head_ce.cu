@@ -11,6 +11,8 @@
 // in CTA order by the last CTA to finish.
 #include "../common.cuh"
 #include "b200seg.h"
+#include <cstdio>
+#include <mutex>
 
 namespace b200 {
 
@@ -245,5 +247,101 @@ extern "C" int b200seg_head_ce(const void* a, long long ld_a, const float* w, co
                                                     grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc,
                                                     ws, counter, warps);
   }
+  return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Allocation-free variant of the head kernel.
+//
+// Who this is for: callers that are not allowed to (or cannot afford to) obtain device memory at
+// call time.  Typical cases: a host application that hands the whole GPU to its own memory pool at
+// start-up and forbids later driver allocations by the code it loads; a latency-critical loop,
+// where cudaMalloc / cudaFree would serialise the entire device and stall every other stream; a
+// plain C program that has no framework allocator to borrow a workspace from.  b200seg_head_ce()
+// needs a caller-provided workspace for its per-CTA partial sums; this entry point needs none,
+// because the partials live in a fixed array that is part of the library image itself.
+//
+// The price: that array (kHeadStaticBytes, about 0.6 MB) is resident on every GPU that loads the
+// library, for the life of the process, whether or not this function is ever called; and the
+// problem size is capped -- C <= 128 channels and K <= 8 classes (any number of pixels).  Larger
+// sizes are refused with cudaErrorInvalidValue and a message on stderr; nothing is launched.
+//
+// All calls on one device share the one array and it keeps whatever the previous call left in it.
+// The only part that has to start at zero, the CTA counter, is cleared on the stream at the start
+// of every call.  Two calls that can run on the GPU at the same time (different streams, or
+// different host threads on different streams) would trample each other's partials: keep calls on
+// one device ordered.  The function never calls cudaMalloc, cudaFree, or any library routine that
+// allocates.
+//
+// First call on each device: the device address of the array is looked up once (with that device
+// current) and cached.  Make that first call during set-up, before any stream capture is begun.
+namespace b200 {
+
+constexpr int kHeadStaticMaxC = 128;
+constexpr int kHeadStaticMaxK = 8;
+constexpr int kHeadStaticBlocks = kNumSMs;                      // one CTA per SM
+constexpr size_t kHeadStaticPartials =
+    (size_t)kHeadStaticBlocks * (kHeadStaticMaxK * kHeadStaticMaxC + kHeadStaticMaxK + 2) * sizeof(float);
+constexpr size_t kHeadStaticBytes = kHeadStaticPartials + 256;  // + the CTA counter
+
+// In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device pointer.
+static __device__ __align__(256) unsigned char g_head_static_scratch[kHeadStaticBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_head_static_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_head_static_mutex;
+
+// Device address of the scratch array on the CURRENT device (resolved once per device).
+static cudaError_t head_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_head_static_mutex);
+  if (g_head_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_head_static_scratch);
+    if (e != cudaSuccess) return e;
+    g_head_static_ptr[dev] = ptr;
+  }
+  *out = g_head_static_ptr[dev];
+  return cudaSuccess;
+}
+
+}  // namespace b200
+
+extern "C" long long b200seg_head_ce_static_scratch_bytes() { return (long long)kHeadStaticBytes; }
+
+extern "C" int b200seg_head_ce_static(const void* a, long long ld_a, const float* w, const float* bias,
+                                      const unsigned char* labels, long long P, int C, int K,
+                                      float grad_scale, void* da, long long ld_da, float* dw, float* db,
+                                      unsigned char* pred, float* loss_acc, cudaStream_t st) {
+  if (C % 8 || C < 8 || K < 1 || P < 1) return (int)cudaErrorInvalidValue;
+  if (C > kHeadStaticMaxC || K > kHeadStaticMaxK) {
+    fprintf(stderr,
+            "b200seg_head_ce_static: C=%d, K=%d do not fit the built-in scratch (limits: C <= %d, K <= %d); "
+            "use b200seg_head_ce with a caller-provided workspace\n",
+            C, K, kHeadStaticMaxC, kHeadStaticMaxK);
+    return (int)cudaErrorInvalidValue;
+  }
+  void* scratch = nullptr;
+  cudaError_t e = head_static_scratch(&scratch);
+  if (e != cudaSuccess) return (int)e;
+  float* partials = reinterpret_cast<float*>(scratch);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(scratch) + kHeadStaticPartials);
+  e = cudaMemsetAsync(counter, 0, 256, st);             // the one thing that must start at zero
+  if (e != cudaSuccess) return (int)e;
+  const int warps = 8, threads = warps * 32;
+  long long chunks = (P + 31) / 32;
+  int grid = (int)((chunks + warps - 1) / warps);
+  if (grid > kHeadStaticBlocks) grid = kHeadStaticBlocks;
+  const int nred = K * C + K + 2;
+  const size_t smem = sizeof(float) * ((size_t)K * C + 8 + ((nred + 3) & ~3) + (size_t)warps * 32 * 8) +
+                      (size_t)warps * 2 * 32 * (C + 8) * 2;
+  e = cudaFuncSetAttribute(head_ce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  head_ce_kernel<8><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K, grad_scale,
+                                                 (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc, partials,
+                                                 counter, warps);
   return (int)cudaGetLastError();
 }

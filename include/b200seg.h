@@ -40,6 +40,22 @@ int b200seg_head_ce(const void* a, long long ld_a, const float* w, const float* 
                     long long ld_da, float* dw, float* db, unsigned char* pred, float* loss_acc,
                     void* workspace, cudaStream_t st);
 
+/* Same computation with NO workspace argument and no allocation of any kind.  (No counterpart in the
+ * reference: it has no device code and no notion of a workspace.)  For callers that must not take
+ * device memory at call time -- hosts that give the whole GPU to their own pool and forbid driver
+ * allocations afterwards, latency-critical loops (cudaMalloc / cudaFree serialise the device), plain C
+ * programs without a framework allocator.  The per-CTA partial sums live in an array built into the
+ * library (b200seg_head_ce_static_scratch_bytes(), ~0.6 MB, resident on every GPU that loads the
+ * library).  Limits: C <= 128, K <= 8; anything larger returns cudaErrorInvalidValue with a message on
+ * stderr and launches nothing.  All calls on a device share that array: calls that may overlap on the
+ * GPU race.  The first call on each device resolves the array's device address; make it before any
+ * stream capture begins. */
+long long b200seg_head_ce_static_scratch_bytes(void);
+int b200seg_head_ce_static(const void* a, long long ld_a, const float* w, const float* bias,
+                           const unsigned char* labels, long long P, int C, int K, float grad_scale,
+                           void* da, long long ld_da, float* dw, float* db, unsigned char* pred,
+                           float* loss_acc, cudaStream_t st);
+
 /* ---- optimizer over the flat buffers: R:704, R:437-438, R:552-553 ------------------------------ */
 int b200seg_fused_adam(float* p, float* g, float* m, float* v, long long n, float lr, float b1, float b2,
                        float eps, float wd, float gscale, float bc1, float bc2, void* p_lowp,
