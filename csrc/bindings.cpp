@@ -246,6 +246,16 @@ void allreduce(at::IntArrayRef wire_ptrs, at::IntArrayRef grad_ptrs, at::IntArra
                        cur()), "allreduce");
 }
 
+void allreduce_nvls(at::IntArrayRef signal_ptrs, int64_t multicast_ptr, int64_t rank, int64_t n_elems,
+                    double post_scale, int64_t epoch, int64_t blocks) {
+  const int world = (int)signal_ptrs.size();
+  TORCH_CHECK(world >= 2 && world <= 16, "allreduce_nvls: bad pointer list");
+  unsigned int* sp[16];
+  for (int r = 0; r < world; ++r) sp[r] = reinterpret_cast<unsigned int*>(signal_ptrs[r]);
+  ok(b200seg_allreduce_nvls(sp, reinterpret_cast<float*>(multicast_ptr), (int)rank, world, n_elems,
+                            (float)post_scale, (unsigned int)epoch, (int)blocks, cur()), "allreduce_nvls");
+}
+
 void write_mult(const Tensor& scale, double levels, Tensor out) {
   c10::cuda::CUDAGuard g(out.device());
   ok(b200seg_write_mult(f32(scale), (float)levels, f32(out), cur()), "write_mult");
@@ -301,6 +311,8 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("allreduce(int[] wire_ptrs, int[] grad_ptrs, int[] signal_ptrs, int[] mult_ptrs, int rank, int n_elems, "
         "int wire_kind, float post_scale, int epoch, Tensor(a!)? oneshot_out, int blocks) -> ()", &allreduce);
   m.def("write_mult(Tensor scale, float levels, Tensor(a!) out) -> ()", &write_mult);
+  m.def("allreduce_nvls(int[] signal_ptrs, int multicast_ptr, int rank, int n_elems, float post_scale, int epoch, "
+        "int blocks) -> ()", &allreduce_nvls);
   m.def("allreduce_signal_bytes() -> int", &allreduce_signal_bytes);
   m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);

@@ -167,6 +167,36 @@ static int launch_ar(const PeerPtrs& pp, int rank, int world, size_t n_elems, fl
 }  // namespace b200
 
 namespace b200 {
+
+// ---- NVLS: in-switch reduction through a multicast mapping -------------------------------------
+// `mc` is the multicast address of the symmetric fp32 gradient buffer (one virtual address that the
+// NVSwitch fans out to every rank's copy).  multimem.ld_reduce makes the SWITCH add the element from
+// all ranks and return the sum; multimem.st writes the result to all ranks.  Rank r does this for
+// slice r only, so every element is reduced once (one owner => identical bits everywhere) and each
+// GPU moves ~S/W bytes in and S/W out instead of (W-1)/W * S each way.
+__global__ void __launch_bounds__(kArThreads)
+allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, size_t n_vec, float post_scale,
+                      uint32_t epoch) {
+  cross_gpu_barrier(pp, rank, world, epoch);
+  const size_t per = (n_vec + world - 1) / world;
+  const size_t v0 = (size_t)rank * per;
+  const size_t v1 = v0 + per < n_vec ? v0 + per : n_vec;
+  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float4 v;
+    float* addr = mc + i * 4;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(addr)
+                 : "memory");
+    v.x *= post_scale; v.y *= post_scale; v.z *= post_scale; v.w *= post_scale;
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+  }
+  cross_gpu_barrier(pp, rank, world, epoch + 1);
+}
+
 __global__ void write_mult_kernel(const float* scale, float levels, float* out) {
   *out = (levels > 0.f) ? __fdiv_rn(*scale, levels) : 1.f;
 }
@@ -209,4 +239,19 @@ extern "C" int b200seg_allreduce(const void* const* wire_ptrs, float* const* gra
     case 4: return launch_ar<__nv_fp8_e4m3>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
   }
   return (int)cudaErrorInvalidValue;
+}
+
+// NVLS variant (fp32 wire only).  `multicast_ptr` comes from the symmetric-memory rendezvous; 0 means
+// the driver / fabric exposes no multicast and the caller must use b200seg_allreduce.
+extern "C" int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* multicast_ptr, int rank, int world,
+                                      long long n_elems, float post_scale, unsigned int epoch, int blocks,
+                                      cudaStream_t st) {
+  if (multicast_ptr == nullptr || world < 2 || world > kMaxRanks || (n_elems % 16) || blocks < 1 ||
+      blocks > b200seg_allreduce_max_blocks())
+    return (int)cudaErrorInvalidValue;
+  PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) pp.signal[r] = signal_ptrs[r];
+  allreduce_nvls_kernel<<<blocks, kArThreads, 0, st>>>(pp, multicast_ptr, rank, world, (size_t)n_elems / 4, post_scale,
+                                                      epoch);
+  return (int)cudaGetLastError();
 }

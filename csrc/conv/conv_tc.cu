@@ -57,6 +57,9 @@ struct TapGemmParams {
   int stages;
   uint32_t a_bytes, b_bytes, stage_bytes, staging_bytes;
   int staging_bufs;                // 1 or 2 output staging tiles (2: TMA store of tile i overlaps tile i+1)
+  int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
+  int xslots;                      // STRIP mode: number of input-strip slots
+  uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
   const float* bias;
   float* partials;
 };
@@ -72,14 +75,22 @@ __device__ __forceinline__ void named_bar_sync(int id, int n) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
 }
 
-template <int BLOCK_K, bool B_MN>
+// STRIP = true (3x3 only, rows >= 128 pixels wide, BLOCK_K = 64): the M tile is 128 consecutive pixels
+// of ONE image row and the activation is loaded as 130-pixel strips (one halo pixel each side), one
+// strip per (filter row, channel chunk).  The three taps of a filter row are UMMA operand windows
+// that start 0, 1 or 2 rows into the strip (the swizzle is a function of the absolute smem address,
+// so any 128-byte row is a legal start) -> activations are fetched 3x instead of 9x from L2.  Strips
+// and weight tiles travel in separate rings.
+template <int BLOCK_K, bool B_MN, bool STRIP>
 __global__ void __launch_bounds__(kConvThreads, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const __grid_constant__ CUtensorMap map_o, const TapGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + (size_t)p.stages * p.stage_bytes;
+  uint8_t* staging = smem + (size_t)p.stages * p.stage_bytes + (STRIP ? (size_t)p.xslots * p.xslot_bytes : 0);
+  uint8_t* const xring = smem + (size_t)p.stages * p.stage_bytes;     // STRIP: strip slots after the B ring
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
+  __shared__ __align__(8) uint64_t bar_xfull[4], bar_xempty[4];
   __shared__ __align__(8) uint64_t bar_tfull[2], bar_tempty[2];
   __shared__ uint32_t tmem_base_s;
   __shared__ float s_bias[256];
@@ -95,8 +106,9 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
+    for (int s = 0; s < 4; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
@@ -114,7 +126,56 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
-    if (elect_one()) {
+    if (STRIP && elect_one()) {
+      int stage = 0, xs = 0;
+      uint32_t phase = 0, xphase = 0;
+      if (p.b_resident) {                                   // the whole filter bank, once
+        mbar_arrive_expect_tx(&bar_full[0], 9 * p.kc_per_tap * p.b_bytes);
+        for (int t = 0; t < 9; ++t)
+          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+            uint8_t* sb = smem + (size_t)(t * p.kc_per_tap + kc) * p.stage_bytes;
+            if (!B_MN) {
+              tma_load_2d(sb, &map_b, &bar_full[0], t * p.kc_total + kc * 64, n_tile * p.block_n);
+            } else {
+              const int nblocks = (p.block_n + 63) >> 6;
+              for (int nb = 0; nb < nblocks; ++nb)
+                tma_load_2d(sb + nb * 8192, &map_b, &bar_full[0],
+                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * 64);
+            }
+          }
+      }
+      for (int m = m_first; m < p.m_tiles; m += m_step) {
+        const int twi = m % p.tiles_w;
+        const int thi = (m / p.tiles_w) % p.tiles_h;
+        const int g = m / (p.tiles_w * p.tiles_h);
+        const int w0 = twi << p.tw_log2, h0 = thi, n0 = g;
+        for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+          for (int r = 0; r < 3; ++r) {
+            MBAR_WAIT_OR_TRAP(&bar_xempty[xs], xphase ^ 1);
+            mbar_arrive_expect_tx(&bar_xfull[xs], 130 * 128);
+            tma_load_4d(xring + (size_t)xs * p.xslot_bytes, &map_a, &bar_xfull[xs], kc * 64, w0 - 1,
+                        h0 + p.flip * (r - 1), n0);
+            if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+            if (p.b_resident) continue;
+            for (int sft = 0; sft < 3; ++sft) {
+              const int t = r * 3 + sft;
+              MBAR_WAIT_OR_TRAP(&bar_empty[stage], phase ^ 1);
+              uint8_t* sb = smem + (size_t)stage * p.stage_bytes;
+              mbar_arrive_expect_tx(&bar_full[stage], p.b_bytes);
+              if (!B_MN) {
+                tma_load_2d(sb, &map_b, &bar_full[stage], t * p.kc_total + kc * 64, n_tile * p.block_n);
+              } else {
+                const int nblocks = (p.block_n + 63) >> 6;
+                for (int nb = 0; nb < nblocks; ++nb)
+                  tma_load_2d(sb + nb * 8192, &map_b, &bar_full[stage],
+                              t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * 64);
+              }
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    } else if (!STRIP && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int m = m_first; m < p.m_tiles; m += m_step) {
@@ -148,7 +209,54 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer ========================================
-    if (elect_one()) {
+    if (STRIP && elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(128, p.block_n, 0, B_MN ? 1 : 0);
+      int stage = 0, xs = 0;
+      uint32_t phase = 0, xphase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      if (p.b_resident) MBAR_WAIT_OR_TRAP(&bar_full[0], 0);
+      for (int m = m_first; m < p.m_tiles; m += m_step) {
+        MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        uint32_t first = 0;
+        for (int kr = 0; kr < p.kc_per_tap * 3; ++kr) {
+          MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
+          tc_fence_after();
+          const uint32_t sx = smem_u32(xring + (size_t)xs * p.xslot_bytes);
+          const uint64_t da_strip = make_smem_desc(sx, 16, 1024, LAYOUT_SW128);
+          const int kc_ = kr / 3, r_ = kr - kc_ * 3;
+#pragma unroll
+          for (int sft = 0; sft < 3; ++sft) {
+            if (!p.b_resident) {
+              MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+              tc_fence_after();
+            }
+            // window of 128 pixel rows starting (1 + flip*(sft-1)) rows into the strip
+            const int win = (p.flip > 0) ? sft : 2 - sft;
+            const uint64_t da0 = da_strip + ((win * 128) >> 4);
+            const int slot = p.b_resident ? ((r_ * 3 + sft) * p.kc_per_tap + kc_) : stage;
+            const uint32_t sb = smem_u32(smem + (size_t)slot * p.stage_bytes);
+            const uint64_t db0 = B_MN ? make_smem_desc(sb, 8192, 1024, LAYOUT_SW128)
+                                      : make_smem_desc(sb, 16, 1024, LAYOUT_SW128);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+              umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc, first);
+              first = 1u;
+            }
+            if (!p.b_resident) {
+              umma_commit(&bar_empty[stage]);
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+          }
+          umma_commit(&bar_xempty[xs]);                    // all three taps of this strip are issued
+          if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+        }
+        umma_commit(&bar_tfull[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    } else if (!STRIP && elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, p.block_n, 0, B_MN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -500,18 +608,24 @@ static int pick_block_n(int n_total, int ocb) {
   return ocb * (256 / ocb >= kMaxGroups ? kMaxGroups : 256 / ocb);
 }
 
-template <int BK, bool BMN>
+template <int BK, bool BMN, bool STRIP = false>
 static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const TapGemmParams& p,
                       int grid, size_t smem, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(tap_gemm_kernel<BK, BMN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(tap_gemm_kernel<BK, BMN, STRIP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(kSmemBudget + 2048));
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
-  tap_gemm_kernel<BK, BMN><<<grid, kConvThreads, smem, st>>>(ma, mb, mo, p);
+  tap_gemm_kernel<BK, BMN, STRIP><<<grid, kConvThreads, smem, st>>>(ma, mb, mo, p);
   return (int)cudaGetLastError();
+}
+
+static int strip_mode_env() {          // B200SEG_CONV_STRIP=0 disables the strip path (benchmarking)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_CONV_STRIP"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return v;
 }
 
 // mode: 0 fprop, 1 dgrad, 2 convT forward, 3 convT data gradient
@@ -522,6 +636,9 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if (BK == 0 || n_total % 16) return (int)cudaErrorInvalidValue;
   TapGemmParams p{};
   TileGeom g = geom_for(N, H, W, 128);
+  // strip mode: 3x3, full 64-channel chunks, rows made of whole 128-pixel segments
+  bool strip = (mode == 0 || mode == 1) && BK == 64 && (W % 128 == 0) && strip_mode_env();
+  if (strip) { g.tw_log2 = 7; g.th_log2 = 0; g.tn = 1; g.tiles_w = W / 128; g.tiles_h = H; g.tiles_g = N; }
   p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
   p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
   p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
@@ -554,10 +671,31 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
   p.staging_bytes = 128u * p.block_n * 2;
   if (p.staging_bytes < 8192) p.staging_bytes = 8192;
-  p.staging_bufs = (2 * p.staging_bytes + 4 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
-  int stages = (int)((kSmemBudget - p.staging_bufs * p.staging_bytes) / p.stage_bytes);
+  if (strip) {
+    p.xslots = 4;
+    p.xslot_bytes = 17 * 1024;                             // 130 rows x 128 B = 16640 -> 17 KiB
+    p.stage_bytes = ((b_raw + 1023) / 1024) * 1024;        // the ring holds weight tiles only
+    const uint32_t fixed = p.xslots * p.xslot_bytes;
+    p.staging_bufs = (fixed + 2 * p.staging_bytes + 6 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
+    if (fixed + p.staging_bufs * p.staging_bytes + 3 * p.stage_bytes > kSmemBudget) strip = false;
+    // small filter banks (64 -> 64) stay resident: no weight traffic after the first tile
+    const uint32_t bank = 9u * p.kc_per_tap * p.stage_bytes;
+    p.b_resident = (strip && p.n_tiles == 1 && fixed + 2 * p.staging_bytes + bank <= kSmemBudget) ? 1 : 0;
+    if (p.b_resident) p.staging_bufs = 2;
+  }
+  if (!strip) {
+    g = geom_for(N, H, W, 128);
+    p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
+    p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
+    p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
+    p.xslots = 0; p.xslot_bytes = 0;
+    p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
+    p.staging_bufs = (2 * p.staging_bytes + 4 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
+  }
+  int stages = (int)((kSmemBudget - p.staging_bufs * p.staging_bytes - p.xslots * p.xslot_bytes) / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return (int)cudaErrorInvalidValue;
+  if (strip && p.b_resident) stages = 9 * p.kc_per_tap;      // smem layout only; no ring barriers are used
   p.stages = stages;
   int grid = kNumSMs - (kNumSMs % p.n_tiles);
   const long long total = (long long)p.m_tiles * p.n_tiles;
@@ -567,7 +705,11 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
 
   CUtensorMap ma, mb, mo;
   const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
-  if (mode != 3) {
+  if (strip) {
+    long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
+    int box[4] = {64, 130, 1, 1};
+    if (!make_map(&ma, a, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+  } else if (mode != 3) {
     long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
     int box[4] = {BK, TW, TH, g.tn};
     if (!make_map(&ma, a, 4, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
@@ -600,7 +742,12 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     int box[5] = {p.ocb, 1, TW, 1, TH * g.tn};
     if (!make_map(&mo, out, 5, dims, str, box, p.ocb * 2)) return (int)cudaErrorInvalidValue;
   }
-  const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.staging_bufs * p.staging_bytes + 1024;
+  const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.xslots * p.xslot_bytes +
+                      (size_t)p.staging_bufs * p.staging_bytes + 1024;
+  if (strip) {
+    if (bmn) return launch_tap<64, true, true>(ma, mb, mo, p, grid, smem, st);
+    return launch_tap<64, false, true>(ma, mb, mo, p, grid, smem, st);
+  }
   if (bmn) {
     if (BK == 64) return launch_tap<64, true>(ma, mb, mo, p, grid, smem, st);
     if (BK == 32) return launch_tap<32, true>(ma, mb, mo, p, grid, smem, st);

@@ -346,7 +346,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
 
 using namespace b200;
 
-extern "C" int b200seg_stats_rows() { return 2 * kNumSMs; }
+extern "C" int b200seg_stats_rows() { return 4 * kNumSMs; }   // CTAs of the reduction kernels (4 per SM)
 
 extern "C" int b200seg_channel_stats(const void* y, long long P, int C, long long ld, float* partial,
                                      int rows, cudaStream_t st) {

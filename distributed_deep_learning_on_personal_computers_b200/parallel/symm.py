@@ -46,7 +46,8 @@ def available(ctx: DistContext) -> bool:
 
 
 class SymmetricAllReduce:
-    def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None):
+    def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None,
+                 algorithm: str = "auto"):
         import torch.distributed._symmetric_memory as symm_mem
         from ..ops import loader
         if loader.library() is None:
@@ -84,8 +85,22 @@ class SymmetricAllReduce:
         self.mult_ptrs = [p + self.mult_off for p in self.sig_ptrs] if codec.needs_scale else []
         self.calls = 0
         self.blocks = int(ops.allreduce_max_blocks())
+        # algorithm: "twoshot" (peer loads/stores), "nvls" (in-switch multimem reduction, fp32 wire),
+        # "oneshot" (small buffers); "auto" = oneshot if tiny, else nvls when B200SEG_NVLS=1 and the
+        # fabric exposes multicast, else twoshot.
+        try:
+            self.multicast_ptr = int(self.h_grad.multicast_ptr or 0)
+        except Exception:
+            self.multicast_ptr = 0
+        import os
+        if algorithm == "auto":
+            algorithm = "nvls" if (os.environ.get("B200SEG_NVLS") == "1" and self.multicast_ptr
+                                   and codec.name == "fp32") else "twoshot"
+        if algorithm == "nvls" and not (self.multicast_ptr and codec.name == "fp32"):
+            raise RuntimeError("NVLS all-reduce needs multicast support and the fp32 codec")
+        self.algorithm = algorithm
         self.oneshot_out: Optional[torch.Tensor] = None
-        if self.n * 4 <= ONESHOT_MAX_BYTES:
+        if self.n * 4 <= ONESHOT_MAX_BYTES and self.algorithm != "nvls" or self.algorithm == "oneshot":
             self.oneshot_out = torch.empty(self.n, dtype=torch.float32, device=dev)
         torch.cuda.synchronize(dev)
         dist.barrier(device_ids=[dev.index])
@@ -113,6 +128,11 @@ class SymmetricAllReduce:
                 Fn._tick()
         epoch = 2 * self.calls + 1
         self.calls += 1
+        if self.algorithm == "nvls":
+            ops.allreduce_nvls(self.sig_ptrs, self.multicast_ptr, self.ctx.rank, self.n, float(post_scale), epoch,
+                               self.blocks)
+            Fn._tick()
+            return self.buffer
         ops.allreduce(self.wire_ptrs, self.grad_ptrs, self.sig_ptrs, self.mult_ptrs, self.ctx.rank, self.n,
                       self.wire_kind, float(post_scale), epoch, self.oneshot_out, self.blocks)
         Fn._tick()

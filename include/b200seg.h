@@ -92,6 +92,12 @@ int b200seg_allreduce(const void* const* wire_ptrs, float* const* grad_ptrs,
                       long long n_elems, int wire_kind, float post_scale, unsigned int epoch,
                       float* oneshot_out, int blocks, cudaStream_t st);
 
+/* NVLS: the NVSwitch performs the addition (multimem.ld_reduce / multimem.st on the multicast mapping of
+ * the symmetric fp32 buffer).  multicast_ptr == NULL -> cudaErrorInvalidValue (use b200seg_allreduce). */
+int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* multicast_ptr, int rank, int world,
+                           long long n_elems, float post_scale, unsigned int epoch, int blocks,
+                           cudaStream_t st);
+
 /* ---- tcgen05 / TMEM / TMA convolutions (csrc/conv): R:579, R:582 (3x3 conv), their autograd
  * backward (dgrad, wgrad), R:607 (ConvTranspose2d k=2 s=2 fused with the concat placement, R:616).
  * Weights are bf16 in the flat-buffer order (Cout,3,3,Cin); dgrad reads them un-transposed as an
