@@ -119,19 +119,27 @@ allreduce_kernel(PeerPtrs pp, int rank, int world, size_t n_vec, float post_scal
     v0 = (size_t)rank * per;
     v1 = v0 + per < n_vec ? v0 + per : n_vec;
   }
+#pragma unroll 2
   for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1;
        i += (size_t)gridDim.x * blockDim.x) {
     float acc[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    float f[kMaxRanks <= 8 ? 8 : 8][V];                 // issue up to 8 peer loads before using any
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {              // fixed order: identical bits on every rank
-      if (r >= world) break;
-      float f[V];
-      Wire<T>::load(pp.wire[r], i, f);
-      const float m = mult[r];
+    for (int r0 = 0; r0 < kMaxRanks; r0 += 8) {
+      if (r0 >= world) break;
 #pragma unroll
-      for (int j = 0; j < V; ++j) acc[j] = fmaf(f[j], m, acc[j]);
+      for (int r = 0; r < 8; ++r)
+        if (r0 + r < world) Wire<T>::load(pp.wire[r0 + r], i, f[r]);
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {                     // fixed order: identical bits on every rank
+        if (r0 + r < world) {
+          const float m = mult[r0 + r];
+#pragma unroll
+          for (int j = 0; j < V; ++j) acc[j] = fmaf(f[r][j], m, acc[j]);
+        }
+      }
     }
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] *= post_scale;
@@ -210,7 +218,7 @@ extern "C" int b200seg_write_mult(const float* scale, float levels, float* out, 
   return (int)cudaGetLastError();
 }
 
-extern "C" int b200seg_allreduce_max_blocks() { return 64; }
+extern "C" int b200seg_allreduce_max_blocks() { return 256; }   // all co-resident: 4 x 512 threads per SM
 extern "C" long long b200seg_allreduce_signal_bytes() {
   return (long long)b200seg_allreduce_max_blocks() * kMaxRanks * sizeof(uint32_t);
 }

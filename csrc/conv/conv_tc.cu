@@ -442,6 +442,7 @@ struct WgradParams {
   int stages;
   uint32_t a_bytes, b_bytes, stage_bytes;
   float* dw;
+  int mt;                                   // M tiles (of 128 rows) per CTA sharing one dy tile: 1 or 2
   int convt;                                // 1: dW[(q, co)][ci] of the 2x2 transposed conv
   int nt_per_q;                             // convT: N tiles per quadrant
   int H;                                    // convT: low-res height (Y = n*H + y)
@@ -474,7 +475,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
     mbar_init(&bar_tfull, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<256>(&tmem_base_s);
+  if (warp == 1) tmem_alloc<512>(&tmem_base_s);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -495,8 +496,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sb = sa + p.a_bytes;
           mbar_arrive_expect_tx(&bar_full[stage], p.a_bytes + p.b_bytes);
-          for (int hb = 0; hb < 2; ++hb) {
-            int blk = m_tile * 2 + hb;
+          for (int hb = 0; hb < 2 * p.mt; ++hb) {
+            int blk = m_tile * 2 * p.mt + hb;
             if (blk >= p.m_blocks) blk = p.m_blocks - 1;     // padding block: loaded, never stored
             const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
             const int dw_ = p.convt ? 0 : (t % 3 - 1), dh_ = p.convt ? 0 : (t / 3 - 1);
@@ -523,11 +524,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
           MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
-          const uint64_t da0 = make_smem_desc(sa, 8192, 1024, LAYOUT_SW128);
           const uint64_t db0 = make_smem_desc(sa + p.a_bytes, 8192, 1024, LAYOUT_SW128);
+          for (int t = 0; t < p.mt; ++t) {                  // the M tiles of this CTA share the dy tile
+            const uint64_t da0 = make_smem_desc(sa + t * 16384, 8192, 1024, LAYOUT_SW128);
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4)
-            umma_bf16(tmem_base, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc, (it | k4) != 0 ? 1u : 0u);
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_bf16(tmem_base + t * 256, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
+                        (it | k4) != 0 ? 1u : 0u);
+          }
           umma_commit(&bar_empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -536,36 +540,38 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
     } else {
       const int rb = warp & 3;
       const int row = rb * 32 + lane;
-      int blk = m_tile * 2 + (row >> 6);
-      const bool blk_ok = blk < p.m_blocks;
-      if (!blk_ok) blk = p.m_blocks - 1;
-      const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
-      const int ci = cc * 64 + (row & 63);
-      const bool row_ok = blk_ok && ci < p.Cin;
       MBAR_WAIT_OR_TRAP(&bar_tfull, 0);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(rb * 32) << 16);
-      float* base = p.dw + (p.convt ? (size_t)0 : (size_t)t * p.Cin) + ci;
       const size_t co_stride = (size_t)p.co_stride;
       const int q = p.convt ? n_tile / p.nt_per_q : 0;
       const int co_base = p.convt ? q * p.Cout + (n_tile % p.nt_per_q) * p.block_n : n_tile * p.block_n;
       const int co_lim = p.convt ? (q + 1) * p.Cout : p.Cout;
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
-        uint32_t r[32];
-        if (p.block_n - c0 >= 32) {
-          tmem_ld_32x32b_x32(t_addr + c0, r);
-        } else {
-          uint32_t r16[16];
-          tmem_ld_32x32b_x16(t_addr + c0, r16);
+      for (int mt = 0; mt < p.mt; ++mt) {
+        int blk = (m_tile * p.mt + mt) * 2 + (row >> 6);
+        const bool blk_ok = blk < p.m_blocks;
+        if (!blk_ok) blk = p.m_blocks - 1;
+        const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
+        const int ci = cc * 64 + (row & 63);
+        const bool row_ok = blk_ok && ci < p.Cin;
+        const uint32_t t_addr = tmem_base + mt * 256 + (static_cast<uint32_t>(rb * 32) << 16);
+        float* base = p.dw + (p.convt ? (size_t)0 : (size_t)t * p.Cin) + ci;
+        for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+          uint32_t r[32];
+          if (p.block_n - c0 >= 32) {
+            tmem_ld_32x32b_x32(t_addr + c0, r);
+          } else {
+            uint32_t r16[16];
+            tmem_ld_32x32b_x16(t_addr + c0, r16);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
-        }
-        tmem_ld_wait();
-        if (row_ok) {
+            for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
+          }
+          tmem_ld_wait();
+          if (row_ok) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int co = co_base + c0 + j;
-            if (c0 + j < p.block_n && co < co_lim) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(r[j]));
+            for (int j = 0; j < 32; ++j) {
+              const int co = co_base + c0 + j;
+              if (c0 + j < p.block_n && co < co_lim) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(r[j]));
+            }
           }
         }
       }
@@ -573,7 +579,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<256>(tmem_base);
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
 // =================================================================================================
@@ -799,7 +805,13 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   p.Cin = Cin; p.Cout = Cout;
   p.chunks_per_tap = (Cin + 63) / 64;
   p.m_blocks = (convt ? 1 : 9) * p.chunks_per_tap;
-  p.m_tiles = (p.m_blocks + 1) / 2;
+  // Optionally two 128-row M tiles per CTA share each dy tile (halves the dy traffic per FLOP, but the
+  // 64 KB stages leave a 3-deep ring).  Measured neutral-to-worse on the U-Net shapes, so it is opt-in:
+  // B200SEG_WGRAD_MT=2.
+  static int mt_env = -1;
+  if (mt_env < 0) { const char* e = getenv("B200SEG_WGRAD_MT"); mt_env = (e != nullptr && e[0] == '2') ? 2 : 1; }
+  p.mt = (mt_env == 2 && p.m_blocks >= 8) ? 2 : 1;
+  p.m_tiles = (p.m_blocks + 2 * p.mt - 1) / (2 * p.mt);
   p.block_n = Cout <= 256 ? Cout : (Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64));
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
   p.nt_per_q = (Cout + p.block_n - 1) / p.block_n;
@@ -808,7 +820,7 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   p.H = H;
   p.co_stride = convt ? Cin : (long long)9 * Cin;
   const int nblocks = (p.block_n + 63) / 64;
-  p.a_bytes = 2 * 8192;
+  p.a_bytes = 2 * p.mt * 8192;
   p.b_bytes = nblocks * 8192;
   p.stage_bytes = p.a_bytes + p.b_bytes;
   int stages = (int)(kSmemBudget / p.stage_bytes);

@@ -84,7 +84,8 @@ class SymmetricAllReduce:
         self.wire_ptrs = [int(p) for p in self.h_wire.buffer_ptrs] if self.h_wire else self.grad_ptrs
         self.mult_ptrs = [p + self.mult_off for p in self.sig_ptrs] if codec.needs_scale else []
         self.calls = 0
-        self.blocks = int(ops.allreduce_max_blocks())
+        per_rank_vecs = self.n // 4 // max(ctx.world_size, 1)
+        self.blocks = int(min(ops.allreduce_max_blocks(), max(8, per_rank_vecs // 1024)))
         # algorithm: "twoshot" (peer loads/stores), "nvls" (in-switch multimem reduction, fp32 wire),
         # "oneshot" (small buffers); "auto" = oneshot if tiny, else nvls when B200SEG_NVLS=1 and the
         # fabric exposes multicast, else twoshot.

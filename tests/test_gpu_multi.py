@@ -51,6 +51,23 @@ def _ar_worker(rank, world, port, q):
                 dist.all_gather(lst, chk)
                 same = all(torch.equal(lst[0], t) for t in lst)
                 out[f"{codec}:{n}:{rep}"] = (err, tol, same)
+        # NVLS (in-switch reduction) when the fabric exposes a multicast mapping
+        x = torch.randn(2_000_000, device="cuda", generator=torch.Generator(device="cuda").manual_seed(7 + rank))
+        probe = symm.SymmetricAllReduce(x, ctx, get_codec("fp32"), algorithm="twoshot")
+        out["multicast"] = bool(probe.multicast_ptr)
+        if probe.multicast_ptr:
+            ar = symm.SymmetricAllReduce(x, ctx, get_codec("fp32"), algorithm="nvls")
+            for rep in range(2):
+                ar.buffer.copy_(x)
+                ar.all_reduce_()
+                got = ar.buffer.clone()
+                ref = x.clone()
+                dist.all_reduce(ref)
+                chk = got.double().sum().reshape(1)
+                lst = [torch.zeros_like(chk) for _ in range(world)]
+                dist.all_gather(lst, chk)
+                out[f"nvls:{rep}"] = ((got - ref).abs().max().item(), 1e-6 + 1e-5 * ref.abs().max().item(),
+                                      all(torch.equal(lst[0], t) for t in lst))
     dist.barrier(device_ids=[rank])
     if rank == 0:
         q.put(out)
@@ -71,6 +88,7 @@ def test_native_allreduce_matches_nccl():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert res.pop("available"), "symmetric memory path not available on this box"
+    print("multicast available:", res.pop("multicast", None))
     for k, (err, tol, same) in res.items():
         assert err <= tol, (k, err, tol)
         assert same, k
