@@ -115,15 +115,29 @@ def timed(fn, steps, dist_ctx, torch):
     return ms
 
 
+def _quiet_stdout():
+    """Route fd 1 to stderr while the benchmark runs (NCCL and friends print banners on stdout) and
+    return a writer for the ONE JSON line the driver expects on the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line: str) -> None:
+        sys.stdout.flush()
+        os.write(real, (line + "\n").encode())
+    return emit
+
+
 def main():
     args = parse()
+    emit = _quiet_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     import torch
     if not torch.cuda.is_available():
         if rank == 0:
-            print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device on this machine"}))
+            emit(json.dumps({"impl": args.impl, "unavailable": "no CUDA device on this machine"}))
         return 0
     torch.cuda.set_device(local)
     if world > 1:
@@ -135,7 +149,7 @@ def main():
     else:
         out = run_own(args, dctx, torch)
     if rank == 0:
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         import torch.distributed as dist
         dist.barrier(device_ids=[local])
@@ -224,7 +238,8 @@ def run_own(args, dctx, torch):
         ms_e2e = timed(step_e2e, args.steps, dctx, torch)
         h2d, d2h = tr.loader.bytes_per_batch, 8
     extra = {"engine": "native", "conv": os.environ.get("B200SEG_CONV", "tcgen05"),
-             "comm": tr.sync.backend, "codec": args.codec, "cuda_graph": not args.no_graph}
+             "comm": tr.sync.backend, "codec": args.codec, "cuda_graph": not args.no_graph,
+             "allreduce": (tr.sync.native.algorithm if tr.sync.native is not None else None)}
     return _result(args, dctx, "own", ms, ms_e2e, clk, launches, h2d, d2h, extra)
 
 

@@ -35,7 +35,9 @@
 
 namespace b200 {
 
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 192;     // wgrad kernels: producer, MMA, 4 epilogue warps
+constexpr int kTapThreads = 320;      // tap GEMM: producer, MMA, 8 epilogue warps (two per TMEM lane quarter)
+constexpr int kEpiThreads = 256;
 constexpr int kMaxStages = 8;
 constexpr int kMaxGroups = 8;
 constexpr uint32_t kSmemBudget = 222 * 1024;
@@ -82,7 +84,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int n) {
 // so any 128-byte row is a legal start) -> activations are fetched 3x instead of 9x from L2.  Strips
 // and weight tiles travel in separate rings.
 template <int BLOCK_K, bool B_MN, bool STRIP>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(kTapThreads, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const __grid_constant__ CUtensorMap map_o, const TapGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -107,13 +109,13 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
     for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
     for (int s = 0; s < 4; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
   if (p.bias != nullptr) {
-    for (int c = threadIdx.x; c < p.block_n; c += kConvThreads) {
+    for (int c = threadIdx.x; c < p.block_n; c += kTapThreads) {
       const int col = (blockIdx.x % p.n_tiles) * p.block_n + c;
       s_bias[c] = (col < p.n_total) ? p.bias[p.out_mode == 1 ? (col % p.convt_cout) : col] : 0.f;
     }
@@ -290,7 +292,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     // ===================================== epilogue ==========================================
     const int rb = warp & 3;                              // TMEM lane quarter this warp may read
     const int row = rb * 32 + lane;                       // tile row (pixel) owned by this thread
-    const int et = threadIdx.x - 64;                      // 0..127 within the epilogue group
+    const int et = threadIdx.x - 64;                      // 0..255 within the epilogue group
+    const int colhalf = (warp - 2) >> 2;                  // two warps share a lane quarter: even / odd 32-column blocks
     const int ocb = p.ocb;
     const int ocb_log2 = (ocb == 64) ? 6 : (ocb == 32 ? 5 : 4);
     const uint32_t row_bytes = ocb * 2;
@@ -301,7 +304,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const int cpr = p.block_n >> 3;                       // chunks per row
     const int st_cc = et % cpr;                           // my chunk column
     const int st_rg = et / cpr;                           // my row group
-    const int st_rstep = 128 / cpr;
+    const int st_rstep = kEpiThreads / cpr;
+    const int st_rows = 128 / st_rstep;                   // rows of the tile this thread sums
     const int st_grp = (st_cc * 8) >> ocb_log2;
     const uint32_t st_chunk = ((st_cc * 8) & (ocb - 1)) >> 3;
     float st_s[8], st_q[8];
@@ -322,7 +326,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + acc * 256 + (static_cast<uint32_t>(rb * 32) << 16);
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+      for (int c0 = colhalf * 32; c0 < p.block_n; c0 += 64) {
         uint32_t r[32];
         if (p.block_n - c0 >= 32) {
           tmem_ld_32x32b_x32(t_addr + c0, r);
@@ -357,12 +361,12 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       mbar_arrive(&bar_tempty[acc]);                      // accumulator drained: MMA may reuse it
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       fence_proxy_async();                                // staging writes -> visible to TMA
-      named_bar_sync(1, 128);
+      named_bar_sync(1, kEpiThreads);
       if (p.partials != nullptr) {
         const bool full_tile = (w0 + TW <= p.W) && (h0 + TH <= p.H) && (n0 + p.tn <= p.N);
         const uint8_t* gb = staging + st_grp * group_bytes;
 #pragma unroll 4
-        for (int i = 0; i < cpr; ++i) {
+        for (int i = 0; i < st_rows; ++i) {
           const int rr = st_rg + i * st_rstep;
           bool valid = true;
           if (!full_tile) {
@@ -393,21 +397,21 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         // the buffer written NEXT must be free: with two buffers that is the store issued one tile ago
         if (p.staging_bufs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1, kEpiThreads);
     }
     if (p.partials != nullptr) {
       // combine the (128 / cpr) threads that share a chunk column, then one row of partials per CTA
       if (et == 0) tma_store_wait_read<0>();
-      named_bar_sync(1, 128);
-      float* red = reinterpret_cast<float*>(staging0);   // [128/cpr][2][block_n]
+      named_bar_sync(1, kEpiThreads);
+      float* red = reinterpret_cast<float*>(staging0);   // [256/cpr][2][block_n]
       const int ncol = p.block_n;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         red[(st_rg * 2 + 0) * ncol + st_cc * 8 + j] = st_s[j];
         red[(st_rg * 2 + 1) * ncol + st_cc * 8 + j] = st_q[j];
       }
-      named_bar_sync(1, 128);
-      for (int c = et; c < ncol; c += 128) {
+      named_bar_sync(1, kEpiThreads);
+      for (int c = et; c < ncol; c += kEpiThreads) {
         float s = 0.f, q = 0.f;
         for (int i = 0; i < st_rstep; ++i) { s += red[(i * 2 + 0) * ncol + c]; q += red[(i * 2 + 1) * ncol + c]; }
         const int col = n_tile * p.block_n + c;
@@ -624,7 +628,7 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
-  tap_gemm_kernel<BK, BMN, STRIP><<<grid, kConvThreads, smem, st>>>(ma, mb, mo, p);
+  tap_gemm_kernel<BK, BMN, STRIP><<<grid, kTapThreads, smem, st>>>(ma, mb, mo, p);
   return (int)cudaGetLastError();
 }
 
@@ -669,14 +673,14 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if ((mode == 2 || mode == 3) && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.bias = bias;
   p.partials = partials;
-  if (partials != nullptr && (128 % (p.block_n / 8) != 0)) return (int)cudaErrorInvalidValue;
+  if (partials != nullptr && (128 % (p.block_n / 8) != 0 || p.block_n < 16)) return (int)cudaErrorInvalidValue;
   p.a_bytes = 128 * BK * 2;
   const bool bmn = (mode == 1 || mode == 3);
   const uint32_t b_raw = bmn ? (uint32_t)((p.block_n + 63) / 64) * 64 * BK * 2 : (uint32_t)p.block_n * BK * 2;
   p.b_bytes = b_raw;
   p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
   p.staging_bytes = 128u * p.block_n * 2;
-  if (p.staging_bytes < 8192) p.staging_bytes = 8192;
+  if (p.staging_bytes < 16384) p.staging_bytes = 16384;
   if (strip) {
     p.xslots = 4;
     p.xslot_bytes = 17 * 1024;                             // 130 rows x 128 B = 16640 -> 17 KiB
@@ -805,11 +809,11 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   p.Cin = Cin; p.Cout = Cout;
   p.chunks_per_tap = (Cin + 63) / 64;
   p.m_blocks = (convt ? 1 : 9) * p.chunks_per_tap;
-  // Optionally two 128-row M tiles per CTA share each dy tile (halves the dy traffic per FLOP, but the
-  // 64 KB stages leave a 3-deep ring).  Measured neutral-to-worse on the U-Net shapes, so it is opt-in:
-  // B200SEG_WGRAD_MT=2.
+  // Two 128-row M tiles per CTA share each dy tile (halves the dy traffic per FLOP).  In isolation it is
+  // neutral, inside the training step it is worth 1.5 ms of 35 (profiles/variants_in_situ.txt), so it
+  // is the default; B200SEG_WGRAD_MT=1 turns it off.
   static int mt_env = -1;
-  if (mt_env < 0) { const char* e = getenv("B200SEG_WGRAD_MT"); mt_env = (e != nullptr && e[0] == '2') ? 2 : 1; }
+  if (mt_env < 0) { const char* e = getenv("B200SEG_WGRAD_MT"); mt_env = (e != nullptr && e[0] == '1') ? 1 : 2; }
   p.mt = (mt_env == 2 && p.m_blocks >= 8) ? 2 : 1;
   p.m_tiles = (p.m_blocks + 2 * p.mt - 1) / (2 * p.mt);
   p.block_n = Cout <= 256 ? Cout : (Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64));

@@ -224,18 +224,40 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
   const long long P = (long long)N * H * W;
   const long long items = POOL ? P / 4 : P;
   const int Wo = W >> 1, Ho = H >> 1;
+  // partial sums per channel: s = sum g, q = sum g*y  (finalize turns q into sum g*xhat)
   float s[8], q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   if (r < rows_pb) {
-    float sc[8], sh[8], mean[8], inv[8];
+    float sc[8], sh[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      sc[j] = ss[cv * 8 + j]; sh[j] = ss[C + cv * 8 + j];
-      mean[j] = ss[2 * C + cv * 8 + j]; inv[j] = ss[3 * C + cv * 8 + j];
+    for (int j = 0; j < 8; ++j) { sc[j] = ss[cv * 8 + j]; sh[j] = ss[C + cv * 8 + j]; }
+    const long long stride = (long long)gridDim.x * rows_pb;
+    long long pix = (long long)blockIdx.x * rows_pb + r;
+    if (!POOL) {
+      // 4 pixels per trip, all eight 16-byte loads issued before any math (memory-level parallelism)
+      for (; pix + 3 * stride < items; pix += 4 * stride) {
+        bf16x8 yy[4], dd[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          yy[u] = ld8(y + (pix + u * stride) * ld_y + cv * 8);
+          if (d_out != nullptr) dd[u] = ld8(d_out + (pix + u * stride) * ld_do + cv * 8);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float yf[8], gf[8];
+          unpack8(yy[u], yf);
+          if (d_out != nullptr) unpack8(dd[u], gf);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float gm = (d_out != nullptr && fmaf(yf[j], sc[j], sh[j]) > 0.f) ? gf[j] : 0.f;
+            s[j] += gm;
+            q[j] = fmaf(gm, yf[j], q[j]);
+          }
+        }
+      }
     }
-    for (long long pix = (long long)blockIdx.x * rows_pb + r; pix < items;
-         pix += (long long)gridDim.x * rows_pb) {
+    for (; pix < items; pix += stride) {
       long long p00 = 0;
       if (POOL) {
         const int wo = (int)(pix % Wo);
@@ -250,7 +272,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           s[j] += g[k][j];
-          q[j] = fmaf(g[k][j], (yv[k][j] - mean[j]) * inv[j], q[j]);
+          q[j] = fmaf(g[k][j], yv[k][j], q[j]);
         }
     }
   }
@@ -284,11 +306,12 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
     sgx += (double)partial[((size_t)r * 2 + 1) * C + c];
   }
   sg = warp_sum_d(sg);
-  sgx = warp_sum_d(sgx);
+  sgx = warp_sum_d(sgx);                               // so far: sum g*y
   if (lane != 0) return;
+  const double mean = ss[2 * C + c], inv = ss[3 * C + c];
+  sgx = inv * (sgx - mean * sg);                       // sum g*xhat
   dbeta[c] += (float)sg;
   dgamma[c] += (float)sgx;
-  const double mean = ss[2 * C + c], inv = ss[3 * C + c];
   const double k1 = (double)gamma[c] * inv;
   const double c1 = sg / (double)count, c2 = sgx / (double)count;
   coef[0 * C + c] = (float)k1;

@@ -151,11 +151,16 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
           av[2 * j] = t.x;
           av[2 * j + 1] = t.y;
         }
+        float dv[KMAX];
+#pragma unroll
+        for (int k = 0; k < KMAX; k += 4) {
+          const float4 t4 = *reinterpret_cast<const float4*>(my_dl + i * KMAX + k);
+          dv[k] = t4.x; dv[k + 1] = t4.y; dv[k + 2] = t4.z; dv[k + 3] = t4.w;
+        }
 #pragma unroll
         for (int k = 0; k < KMAX; ++k) {
-          const float d = my_dl[i * KMAX + k];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) accw[k][j] = fmaf(d, av[j], accw[k][j]);
+          for (int j = 0; j < 8; ++j) accw[k][j] = fmaf(dv[k], av[j], accw[k][j]);
         }
       }
     }

@@ -87,15 +87,17 @@ class SymmetricAllReduce:
         per_rank_vecs = self.n // 4 // max(ctx.world_size, 1)
         self.blocks = int(min(ops.allreduce_max_blocks(), max(8, per_rank_vecs // 1024)))
         # algorithm: "twoshot" (peer loads/stores), "nvls" (in-switch multimem reduction, fp32 wire),
-        # "oneshot" (small buffers); "auto" = oneshot if tiny, else nvls when B200SEG_NVLS=1 and the
-        # fabric exposes multicast, else twoshot.
+        # "oneshot" (small buffers); "auto" = nvls when the fabric exposes multicast (fp32 wire), else
+        # oneshot if tiny, else twoshot.
         try:
             self.multicast_ptr = int(self.h_grad.multicast_ptr or 0)
         except Exception:
             self.multicast_ptr = 0
         import os
         if algorithm == "auto":
-            algorithm = "nvls" if (os.environ.get("B200SEG_NVLS") == "1" and self.multicast_ptr
+            # NVLS measured fastest at every size on 8 GPUs (profiles/allreduce_sweep_8gpu.txt);
+            # B200SEG_NVLS=0 forces the peer load/store kernels.
+            algorithm = "nvls" if (os.environ.get("B200SEG_NVLS", "1") != "0" and self.multicast_ptr
                                    and codec.name == "fp32") else "twoshot"
         if algorithm == "nvls" and not (self.multicast_ptr and codec.name == "fp32"):
             raise RuntimeError("NVLS all-reduce needs multicast support and the fp32 codec")
