@@ -126,6 +126,24 @@ bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ y, long long ld_y,
       last_cv = cv;
     }
     if (!POOL) {
+      // when the grid stride is a multiple of CV the channel group is the same for the next trips:
+      // issue four loads before any math
+      const long long gs = (long long)gridDim.x * blockDim.x;
+      if (gs % CV == 0 && idx + 3 * gs < items) {
+        bf16x8 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = ld8(y + ((idx + u * gs) / CV) * ld_y + cv * 8);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float f[8];
+          unpack8(v[u], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+          st8(out + ((idx + u * gs) / CV) * ld_o + cv * 8, pack8(f));
+        }
+        idx += 3 * gs;
+        continue;
+      }
       float f[8];
       unpack8(ld8(y + pix * ld_y + cv * 8), f);
 #pragma unroll
@@ -344,6 +362,29 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
         e0[j] = __ldg(coef + 2 * C + cv * 8 + j);
       }
       last_cv = cv;
+    }
+    if (!POOL) {
+      const long long gs = (long long)gridDim.x * blockDim.x;
+      if (gs % CV == 0 && idx + gs < items) {              // two pixels per trip, loads first
+        const long long px1 = (idx + gs) / CV;
+        const bf16x8 y0 = ld8(y + pix * ld_y + cv * 8), y1 = ld8(y + px1 * ld_y + cv * 8);
+        bf16x8 d0 = y0, d1 = y1;
+        if (d_out != nullptr) { d0 = ld8(d_out + pix * ld_do + cv * 8); d1 = ld8(d_out + px1 * ld_do + cv * 8); }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          float yf[8], gf[8], o[8];
+          unpack8(u ? y1 : y0, yf);
+          unpack8(u ? d1 : d0, gf);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float gm = (d_out != nullptr && fmaf(yf[j], sc[j], sh[j]) > 0.f) ? gf[j] : 0.f;
+            o[j] = fmaf(k1[j], gm, fmaf(e1[j], yf[j], e0[j]));
+          }
+          st8(dy + (u ? px1 : pix) * ld_dy + cv * 8, pack8(o));
+        }
+        idx += gs;
+        continue;
+      }
     }
     long long p00 = 0;
     if (POOL) {
