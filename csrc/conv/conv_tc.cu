@@ -59,6 +59,7 @@ struct TapGemmParams {
   int stages;
   uint32_t a_bytes, b_bytes, stage_bytes, staging_bytes;
   int staging_bufs;                // 1 or 2 output staging tiles (2: TMA store of tile i overlaps tile i+1)
+  int cluster;                     // 1, or 2: CTA pairs (adjacent M tiles) share the weight tile via TMA multicast
   int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
   int xslots;                      // STRIP mode: number of input-strip slots
   uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
@@ -99,16 +100,26 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int n_tile = blockIdx.x % p.n_tiles;
-  const int m_first = blockIdx.x / p.n_tiles;
-  const int m_step = gridDim.x / p.n_tiles;
+  // Scheduling unit = cluster (1 or 2 CTAs).  A cluster walks "units" of `csz` adjacent M tiles with one
+  // N tile; CTA `crank` takes tile unit*csz + crank.  Every CTA of a cluster runs the same number of
+  // iterations (a CTA past the end re-computes the last tile and stores nothing) so that the shared
+  // weight-tile pipeline stays in lock step.
+  const int csz = p.cluster;
+  const int crank = (csz == 2) ? (int)cluster_ctarank() : 0;
+  const uint16_t cmask = (uint16_t)((1u << csz) - 1);
+  const int unit0 = blockIdx.x / csz;
+  const int n_tile = unit0 % p.n_tiles;
+  const int m_first = unit0 / p.n_tiles;
+  const int m_step = (gridDim.x / csz) / p.n_tiles;
+  const int m_units = (p.m_tiles + csz - 1) / csz;
+  const int prow = m_first * csz + crank;                 // this CTA's row of the statistics partials
   const int TW = 1 << p.tw_log2, TH = 1 << p.th_log2;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
-    for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], csz); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
     for (int s = 0; s < 4; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
     fence_barrier_init();
@@ -122,9 +133,32 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (csz == 2) cluster_sync_all();                       // peers' barriers exist before anything multicasts
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
   const int k_iters = p.taps * p.kc_per_tap;
+  // weight-tile loader: a lone CTA fetches the whole tile; in a pair each CTA fetches half and
+  // multicasts it into both (the full barrier of each CTA still expects the whole tile)
+  auto load_b = [&](uint8_t* sb, uint64_t* bar, int t, int kc) {
+    if (!B_MN) {
+      const int half = p.block_n / csz;
+      if (csz == 1) tma_load_2d(sb, &map_b, bar, t * p.kc_total + kc * BLOCK_K, n_tile * p.block_n);
+      else tma_load_2d_mc(sb + (size_t)crank * half * (BLOCK_K * 2), &map_b, bar, t * p.kc_total + kc * BLOCK_K,
+                          n_tile * p.block_n + crank * half, cmask);
+    } else {
+      const int nblocks = (p.block_n + 63) >> 6;
+      for (int nb = 0; nb < nblocks; ++nb) {
+        const int c0 = t * p.b_tap_stride + n_tile * p.block_n + nb * 64;
+        const int c1 = t * p.b_row_tap_stride + kc * BLOCK_K;
+        if (csz == 1) tma_load_2d(sb + nb * (BLOCK_K * 128), &map_b, bar, c0, c1);
+        else if ((nb & 1) == crank || (nblocks == 1 && crank == 0))
+          tma_load_2d_mc(sb + nb * (BLOCK_K * 128), &map_b, bar, c0, c1, cmask);
+      }
+    }
+  };
+  auto release_b = [&](uint64_t* bar) {
+    if (csz == 1) umma_commit(bar); else umma_commit_mc(bar, cmask);
+  };
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -134,19 +168,11 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       if (p.b_resident) {                                   // the whole filter bank, once
         mbar_arrive_expect_tx(&bar_full[0], 9 * p.kc_per_tap * p.b_bytes);
         for (int t = 0; t < 9; ++t)
-          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
-            uint8_t* sb = smem + (size_t)(t * p.kc_per_tap + kc) * p.stage_bytes;
-            if (!B_MN) {
-              tma_load_2d(sb, &map_b, &bar_full[0], t * p.kc_total + kc * 64, n_tile * p.block_n);
-            } else {
-              const int nblocks = (p.block_n + 63) >> 6;
-              for (int nb = 0; nb < nblocks; ++nb)
-                tma_load_2d(sb + nb * 8192, &map_b, &bar_full[0],
-                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * 64);
-            }
-          }
+          for (int kc = 0; kc < p.kc_per_tap; ++kc)
+            load_b(smem + (size_t)(t * p.kc_per_tap + kc) * p.stage_bytes, &bar_full[0], t, kc);
       }
-      for (int m = m_first; m < p.m_tiles; m += m_step) {
+      for (int mu = m_first; mu < m_units; mu += m_step) {
+        const int m = min(mu * csz + crank, p.m_tiles - 1);
         const int twi = m % p.tiles_w;
         const int thi = (m / p.tiles_w) % p.tiles_h;
         const int g = m / (p.tiles_w * p.tiles_h);
@@ -162,16 +188,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             for (int sft = 0; sft < 3; ++sft) {
               const int t = r * 3 + sft;
               MBAR_WAIT_OR_TRAP(&bar_empty[stage], phase ^ 1);
-              uint8_t* sb = smem + (size_t)stage * p.stage_bytes;
               mbar_arrive_expect_tx(&bar_full[stage], p.b_bytes);
-              if (!B_MN) {
-                tma_load_2d(sb, &map_b, &bar_full[stage], t * p.kc_total + kc * 64, n_tile * p.block_n);
-              } else {
-                const int nblocks = (p.block_n + 63) >> 6;
-                for (int nb = 0; nb < nblocks; ++nb)
-                  tma_load_2d(sb + nb * 8192, &map_b, &bar_full[stage],
-                              t * p.b_tap_stride + n_tile * p.block_n + nb * 64, kc * 64);
-              }
+              load_b(smem + (size_t)stage * p.stage_bytes, &bar_full[stage], t, kc);
               if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
           }
@@ -180,7 +198,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     } else if (!STRIP && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int m = m_first; m < p.m_tiles; m += m_step) {
+      for (int mu = m_first; mu < m_units; mu += m_step) {
+        const int m = min(mu * csz + crank, p.m_tiles - 1);
         const int twi = m % p.tiles_w;
         const int thi = (m / p.tiles_w) % p.tiles_h;
         const int g = m / (p.tiles_w * p.tiles_h);
@@ -195,15 +214,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             mbar_arrive_expect_tx(&bar_full[stage], p.a_bytes + p.b_bytes);
             if (p.a_mode == 0) tma_load_4d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, w0 + dw, h0 + dh, n0);
             else tma_load_5d(sa, &map_a, &bar_full[stage], kc * BLOCK_K, t & 1, w0, t >> 1, n0 * p.H + h0);
-            if (!B_MN) {
-              tma_load_2d(sb, &map_b, &bar_full[stage], t * p.kc_total + kc * BLOCK_K, n_tile * p.block_n);
-            } else {
-              const int nblocks = (p.block_n + 63) >> 6;
-              for (int nb = 0; nb < nblocks; ++nb)
-                tma_load_2d(sb + nb * (BLOCK_K * 128), &map_b, &bar_full[stage],
-                            t * p.b_tap_stride + n_tile * p.block_n + nb * 64,
-                            t * p.b_row_tap_stride + kc * BLOCK_K);
-            }
+            load_b(sb, &bar_full[stage], t, kc);
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -218,7 +229,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       int acc = 0;
       uint32_t acc_phase = 0;
       if (p.b_resident) MBAR_WAIT_OR_TRAP(&bar_full[0], 0);
-      for (int m = m_first; m < p.m_tiles; m += m_step) {
+      for (int mu = m_first; mu < m_units; mu += m_step) {
+        const int m = min(mu * csz + crank, p.m_tiles - 1);
         MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -248,7 +260,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
               first = 1u;
             }
             if (!p.b_resident) {
-              umma_commit(&bar_empty[stage]);
+              release_b(&bar_empty[stage]);
               if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
           }
@@ -264,7 +276,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int m = m_first; m < p.m_tiles; m += m_step) {
+      for (int mu = m_first; mu < m_units; mu += m_step) {
+        const int m = min(mu * csz + crank, p.m_tiles - 1);
         MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -281,7 +294,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
             umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc,
                       (it | k4) != 0 ? 1u : 0u);
-          umma_commit(&bar_empty[stage]);                 // frees the smem stage when the MMAs retire
+          release_b(&bar_empty[stage]);                   // frees the smem stage (in both CTAs of a pair)
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
         umma_commit(&bar_tfull[acc]);                     // accumulator complete
@@ -316,7 +329,9 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint32_t acc_phase = 0;
     int sbuf = 0;
     uint8_t* const staging0 = staging;
-    for (int m = m_first; m < p.m_tiles; m += m_step) {
+    for (int mu = m_first; mu < m_units; mu += m_step) {
+      const bool live = mu * csz + crank < p.m_tiles;
+      const int m = min(mu * csz + crank, p.m_tiles - 1);
       uint8_t* const staging = staging0 + (size_t)sbuf * p.staging_bytes;     // this tile's staging buffer
       if (p.staging_bufs == 2) sbuf ^= 1;
       const int twi = m % p.tiles_w;
@@ -362,7 +377,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       fence_proxy_async();                                // staging writes -> visible to TMA
       named_bar_sync(1, kEpiThreads);
-      if (p.partials != nullptr) {
+      if (p.partials != nullptr && live) {
         const bool full_tile = (w0 + TW <= p.W) && (h0 + TH <= p.H) && (n0 + p.tn <= p.N);
         const uint8_t* gb = staging + st_grp * group_bytes;
 #pragma unroll 4
@@ -383,7 +398,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           }
         }
       }
-      if (et == 0) {
+      if (et == 0 && live) {
         for (int g = 0; g < p.groups; ++g) {
           const int ch0 = n_tile * p.block_n + g * ocb;
           if (p.out_mode == 0) {
@@ -393,6 +408,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             tma_store_5d(&map_o, staging + g * group_bytes, co0, q & 1, w0, q >> 1, n0 * p.H + h0);
           }
         }
+      }
+      if (et == 0) {
         tma_store_commit();
         // the buffer written NEXT must be free: with two buffers that is the store issued one tile ago
         if (p.staging_bufs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
@@ -416,8 +433,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int i = 0; i < st_rstep; ++i) { s += red[(i * 2 + 0) * ncol + c]; q += red[(i * 2 + 1) * ncol + c]; }
         const int col = n_tile * p.block_n + c;
         if (col < p.n_total) {
-          p.partials[((size_t)m_first * 2 + 0) * p.n_total + col] = s;
-          p.partials[((size_t)m_first * 2 + 1) * p.n_total + col] = q;
+          p.partials[((size_t)prow * 2 + 0) * p.n_total + col] = s;
+          p.partials[((size_t)prow * 2 + 1) * p.n_total + col] = q;
         }
       }
     }
@@ -425,6 +442,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (csz == 2) cluster_sync_all();                       // no CTA leaves while its peer may still write to it
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
@@ -628,8 +646,29 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
-  tap_gemm_kernel<BK, BMN, STRIP><<<grid, kTapThreads, smem, st>>>(ma, mb, mo, p);
-  return (int)cudaGetLastError();
+  if (p.cluster == 1) {
+    tap_gemm_kernel<BK, BMN, STRIP><<<grid, kTapThreads, smem, st>>>(ma, mb, mo, p);
+    return (int)cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kTapThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, tap_gemm_kernel<BK, BMN, STRIP>, ma, mb, mo, p);
+}
+
+static int cluster_env() {             // B200SEG_CLUSTER=1 enables CTA-pair weight multicast (off by default)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_CLUSTER"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  return v;
 }
 
 static int strip_mode_env() {          // B200SEG_CONV_STRIP=0 disables the strip path (benchmarking)
@@ -707,8 +746,18 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if (stages < 2) return (int)cudaErrorInvalidValue;
   if (strip && p.b_resident) stages = 9 * p.kc_per_tap;      // smem layout only; no ring barriers are used
   p.stages = stages;
-  int grid = kNumSMs - (kNumSMs % p.n_tiles);
-  const long long total = (long long)p.m_tiles * p.n_tiles;
+  // CTA pairs (clusters of 2 along M) can share each weight tile through TMA multicast, halving the
+  // weight traffic from L2.  Implemented and correct (tests pass with B200SEG_CLUSTER=1) but measured
+  // SLOWER on B200 for these shapes (L0.dec0 fprop 1.66 -> 2.08 ms, whole step 34.4 -> 35.0 ms): the
+  // pair runs in lock step and the 8 x 8 KB weight ring is too shallow to hide the coupled latency.
+  // Kept as an opt-in experiment (profiles/variants_in_situ.txt).
+  p.cluster = 1;
+  if (cluster_env() && mode != 2 && mode != 3 && p.m_tiles >= 2 * kNumSMs && (p.block_n % 32 == 0) &&
+      (bmn ? true : (p.block_n / 2) % 8 == 0))
+    p.cluster = 2;
+  const int unit = p.n_tiles * p.cluster;
+  int grid = kNumSMs - (kNumSMs % unit);
+  const long long total = (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
   if (total < grid) grid = (int)total;
   if (stat_rows_out) *stat_rows_out = grid / p.n_tiles;
   if (dry) return 0;
@@ -731,7 +780,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   }
   if (!bmn) {      // weights as [n_total rows][taps*Kc cols], K contiguous
     long long dims[2] = {(long long)p.taps * Kc, n_total}, str[2] = {1, (long long)p.taps * Kc};
-    int box[2] = {BK, p.block_n};
+    int box[2] = {BK, p.block_n / p.cluster};               // a CTA pair loads half a tile each
     if (!make_map(&mb, w, 2, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
   } else if (mode == 3) {   // transposed-conv weights [(q, co) rows][ci cols], N = ci contiguous
     long long dims[2] = {n_total, (long long)4 * Kc}, str[2] = {1, n_total};
