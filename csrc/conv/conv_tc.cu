@@ -40,6 +40,8 @@ constexpr int kTapThreads = 320;      // tap GEMM: producer, MMA, 8 epilogue war
 constexpr int kEpiThreads = 256;
 constexpr int kMaxStages = 8;
 constexpr int kMaxGroups = 8;
+constexpr int kClusterSize = 1;       // 1 | 2 (experiment, slower: profiles/variants_in_situ.txt)
+constexpr int kMaxXSlots = 16;        // strip ring: TMA latency (~1.5 us) needs several tiles of strips in flight
 constexpr uint32_t kSmemBudget = 222 * 1024;
 
 struct TapGemmParams {
@@ -93,7 +95,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   uint8_t* staging = smem + (size_t)p.stages * p.stage_bytes + (STRIP ? (size_t)p.xslots * p.xslot_bytes : 0);
   uint8_t* const xring = smem + (size_t)p.stages * p.stage_bytes;     // STRIP: strip slots after the B ring
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
-  __shared__ __align__(8) uint64_t bar_xfull[4], bar_xempty[4];
+  __shared__ __align__(8) uint64_t bar_xfull[kMaxXSlots], bar_xempty[kMaxXSlots];
   __shared__ __align__(8) uint64_t bar_tfull[2], bar_tempty[2];
   __shared__ uint32_t tmem_base_s;
   __shared__ float s_bias[256];
@@ -104,7 +106,10 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   // N tile; CTA `crank` takes tile unit*csz + crank.  Every CTA of a cluster runs the same number of
   // iterations (a CTA past the end re-computes the last tile and stores nothing) so that the shared
   // weight-tile pipeline stays in lock step.
-  const int csz = p.cluster;
+  // Compile-time switch: 2 enables the CTA-pair weight multicast experiment (see run_tap_gemm).  As a
+  // run-time value the extra branches cost the MN-major (dgrad) producer 12-30 % (A/B in
+  // profiles/variants_in_situ.txt), so it is a constant.
+  constexpr int csz = kClusterSize;
   const int crank = (csz == 2) ? (int)cluster_ctarank() : 0;
   const uint16_t cmask = (uint16_t)((1u << csz) - 1);
   const int unit0 = blockIdx.x / csz;
@@ -121,7 +126,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     tma_prefetch_desc(&map_o);
     for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], csz); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
-    for (int s = 0; s < 4; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
+    for (int s = 0; s < kMaxXSlots; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
@@ -180,8 +185,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int kc = 0; kc < p.kc_per_tap; ++kc) {
           for (int r = 0; r < 3; ++r) {
             MBAR_WAIT_OR_TRAP(&bar_xempty[xs], xphase ^ 1);
-            mbar_arrive_expect_tx(&bar_xfull[xs], 130 * 128);
-            tma_load_4d(xring + (size_t)xs * p.xslot_bytes, &map_a, &bar_xfull[xs], kc * 64, w0 - 1,
+            mbar_arrive_expect_tx(&bar_xfull[xs], 130 * KCfg<BLOCK_K>::kRowBytes);
+            tma_load_4d(xring + (size_t)xs * p.xslot_bytes, &map_a, &bar_xfull[xs], kc * BLOCK_K, w0 - 1,
                         h0 + p.flip * (r - 1), n0);
             if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
             if (p.b_resident) continue;
@@ -239,7 +244,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
           tc_fence_after();
           const uint32_t sx = smem_u32(xring + (size_t)xs * p.xslot_bytes);
-          const uint64_t da_strip = make_smem_desc(sx, 16, 1024, LAYOUT_SW128);
+          const uint64_t da_strip = make_smem_desc(sx, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
           const int kc_ = kr / 3, r_ = kr - kc_ * 3;
 #pragma unroll
           for (int sft = 0; sft < 3; ++sft) {
@@ -249,13 +254,13 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             }
             // window of 128 pixel rows starting (1 + flip*(sft-1)) rows into the strip
             const int win = (p.flip > 0) ? sft : 2 - sft;
-            const uint64_t da0 = da_strip + ((win * 128) >> 4);
+            const uint64_t da0 = da_strip + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
             const int slot = p.b_resident ? ((r_ * 3 + sft) * p.kc_per_tap + kc_) : stage;
             const uint32_t sb = smem_u32(smem + (size_t)slot * p.stage_bytes);
-            const uint64_t db0 = B_MN ? make_smem_desc(sb, 8192, 1024, LAYOUT_SW128)
-                                      : make_smem_desc(sb, 16, 1024, LAYOUT_SW128);
+            const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
+                                      : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
 #pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) {
+            for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
               umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc, first);
               first = 1u;
             }
@@ -303,6 +308,10 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
   } else {
     // ===================================== epilogue ==========================================
+    // The epilogue is instruction-issue bound for the narrow (N = 64) layers, so everything that does
+    // not depend on the tile is hoisted: per-thread staging addresses, the statistics addresses, and
+    // the tile-coordinate divisions (only the one thread that issues the TMA store needs them unless
+    // the layer has ragged tiles).
     const int rb = warp & 3;                              // TMEM lane quarter this warp may read
     const int row = rb * 32 + lane;                       // tile row (pixel) owned by this thread
     const int et = threadIdx.x - 64;                      // 0..255 within the epilogue group
@@ -312,8 +321,11 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const uint32_t row_bytes = ocb * 2;
     const uint32_t swz_mask = (row_bytes >> 4) - 1;       // 16-byte chunks per row - 1
     const uint32_t group_bytes = 128 * row_bytes;
+    // swizzle<B,4,3>: chunk index XOR (row-derived constant); the XOR term only depends on the row
+    const uint32_t my_row_off = row * row_bytes;
+    const uint32_t my_rx = (my_row_off >> 7) & swz_mask;
     // statistics: this thread owns ONE 16-byte chunk column (8 channels) of the N tile and walks
-    // CPR of the 128 rows; requires block_n / 8 to divide 128 (power-of-two Cout).
+    // st_rows of the 128 rows; requires block_n / 8 to divide 128 (power-of-two Cout).
     const int cpr = p.block_n >> 3;                       // chunks per row
     const int st_cc = et % cpr;                           // my chunk column
     const int st_rg = et / cpr;                           // my row group
@@ -325,25 +337,24 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 #pragma unroll
     for (int j = 0; j < 8; ++j) st_s[j] = st_q[j] = 0.f;
     const bool has_bias = p.bias != nullptr;
+    const bool want_stats = p.partials != nullptr;
+    const bool ragged = ((p.W & (TW - 1)) | (p.H & (TH - 1))) != 0 || (p.N % p.tn) != 0;
+    const int block_n = p.block_n;
     int acc = 0;
     uint32_t acc_phase = 0;
     int sbuf = 0;
     uint8_t* const staging0 = staging;
     for (int mu = m_first; mu < m_units; mu += m_step) {
       const bool live = mu * csz + crank < p.m_tiles;
-      const int m = min(mu * csz + crank, p.m_tiles - 1);
       uint8_t* const staging = staging0 + (size_t)sbuf * p.staging_bytes;     // this tile's staging buffer
       if (p.staging_bufs == 2) sbuf ^= 1;
-      const int twi = m % p.tiles_w;
-      const int thi = (m / p.tiles_w) % p.tiles_h;
-      const int g_img = m / (p.tiles_w * p.tiles_h);
-      const int w0 = twi << p.tw_log2, h0 = thi << p.th_log2, n0 = g_img * p.tn;
       MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + acc * 256 + (static_cast<uint32_t>(rb * 32) << 16);
-      for (int c0 = colhalf * 32; c0 < p.block_n; c0 += 64) {
+      for (int c0 = colhalf * 32; c0 < block_n; c0 += 64) {
         uint32_t r[32];
-        if (p.block_n - c0 >= 32) {
+        const bool wide = block_n - c0 >= 32;
+        if (wide) {
           tmem_ld_32x32b_x32(t_addr + c0, r);
         } else {
           uint32_t r16[16];
@@ -352,10 +363,12 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
         }
         tmem_ld_wait();
-        const int ncols = (p.block_n - c0 >= 32) ? 32 : 16;
+        // the 32 columns lie inside one group when ocb >= 32; for ocb == 16 they span two groups
+        uint8_t* const gbase = staging + (c0 >> ocb_log2) * group_bytes + my_row_off;
+        const uint32_t ch0 = (c0 & (ocb - 1)) >> 3;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {                     // four 16-byte chunks of 8 channels
-          if (v * 8 < ncols) {
+          if (wide || v < 2) {
             float f[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
@@ -363,12 +376,10 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 #pragma unroll
               for (int j = 0; j < 8; ++j) f[j] += s_bias[c0 + v * 8 + j];
             }
-            const int cg = c0 + v * 8;                    // column within the N tile
-            const int grp = cg >> ocb_log2;
-            const uint32_t chunk = (cg & (ocb - 1)) >> 3;
-            const uint32_t off = row * row_bytes + (chunk << 4);
-            const uint32_t phys = off ^ (((off >> 7) & swz_mask) << 4);
-            *reinterpret_cast<bf16x8*>(staging + grp * group_bytes + phys) = pack8(f);
+            uint32_t chunk = ch0 + v;
+            uint8_t* gb = gbase;
+            if (ocb == 16 && v >= 2) { chunk -= 2; gb += group_bytes; }
+            *reinterpret_cast<bf16x8*>(gb + ((chunk ^ my_rx) << 4)) = pack8(f);
           }
         }
       }
@@ -377,30 +388,43 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       fence_proxy_async();                                // staging writes -> visible to TMA
       named_bar_sync(1, kEpiThreads);
-      if (p.partials != nullptr && live) {
-        const bool full_tile = (w0 + TW <= p.W) && (h0 + TH <= p.H) && (n0 + p.tn <= p.N);
+      int w0 = 0, h0 = 0, n0 = 0;
+      if (et == 0 || (ragged && want_stats)) {            // tile coordinates: integer divisions, off the hot path
+        const int m = min(mu * csz + crank, p.m_tiles - 1);
+        const int twi = m % p.tiles_w;
+        const int thi = (m / p.tiles_w) % p.tiles_h;
+        const int g_img = m / (p.tiles_w * p.tiles_h);
+        w0 = twi << p.tw_log2; h0 = thi << p.th_log2; n0 = g_img * p.tn;
+      }
+      if (want_stats && live) {
         const uint8_t* gb = staging + st_grp * group_bytes;
+        if (!ragged) {
 #pragma unroll 4
-        for (int i = 0; i < st_rows; ++i) {
-          const int rr = st_rg + i * st_rstep;
-          bool valid = true;
-          if (!full_tile) {
-            const int tw_ = rr & (TW - 1), th_ = (rr >> p.tw_log2) & (TH - 1), tn_ = rr >> (p.tw_log2 + p.th_log2);
-            valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
-          }
-          const uint32_t off = rr * row_bytes + (st_chunk << 4);
-          const uint32_t phys = off ^ (((off >> 7) & swz_mask) << 4);
-          float f[8];
-          unpack8(*reinterpret_cast<const bf16x8*>(gb + phys), f);
-          if (valid) {
+          for (int i = 0; i < st_rows; ++i) {
+            const uint32_t ro = (st_rg + i * st_rstep) * row_bytes;
+            float f[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
 #pragma unroll
             for (int j = 0; j < 8; ++j) { st_s[j] += f[j]; st_q[j] = fmaf(f[j], f[j], st_q[j]); }
+          }
+        } else {
+          for (int i = 0; i < st_rows; ++i) {
+            const int rr = st_rg + i * st_rstep;
+            const int tw_ = rr & (TW - 1), th_ = (rr >> p.tw_log2) & (TH - 1), tn_ = rr >> (p.tw_log2 + p.th_log2);
+            const bool valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
+            const uint32_t ro = rr * row_bytes;
+            float f[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
+            if (valid) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) { st_s[j] += f[j]; st_q[j] = fmaf(f[j], f[j], st_q[j]); }
+            }
           }
         }
       }
       if (et == 0 && live) {
         for (int g = 0; g < p.groups; ++g) {
-          const int ch0 = n_tile * p.block_n + g * ocb;
+          const int ch0 = n_tile * block_n + g * ocb;
           if (p.out_mode == 0) {
             tma_store_4d(&map_o, staging + g * group_bytes, ch0, w0, h0, n0);
           } else {
@@ -686,7 +710,8 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   TapGemmParams p{};
   TileGeom g = geom_for(N, H, W, 128);
   // strip mode: 3x3, full 64-channel chunks, rows made of whole 128-pixel segments
-  bool strip = (mode == 0 || mode == 1) && BK == 64 && (W % 128 == 0) && strip_mode_env();
+  bool strip = (mode == 0 || mode == 1) && (BK == 64 || (BK == 16 && mode == 0)) && (W % 128 == 0) &&
+               strip_mode_env();
   if (strip) { g.tw_log2 = 7; g.th_log2 = 0; g.tn = 1; g.tiles_w = W / 128; g.tiles_h = H; g.tiles_g = N; }
   p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
   p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
@@ -721,16 +746,27 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.staging_bytes = 128u * p.block_n * 2;
   if (p.staging_bytes < 16384) p.staging_bytes = 16384;
   if (strip) {
-    p.xslots = 4;
-    p.xslot_bytes = 17 * 1024;                             // 130 rows x 128 B = 16640 -> 17 KiB
+    p.xslot_bytes = ((130u * BK * 2 + 1023) / 1024) * 1024;  // 130 rows of one K chunk (16640 B -> 17 KiB at BK=64)
     p.stage_bytes = ((b_raw + 1023) / 1024) * 1024;        // the ring holds weight tiles only
-    const uint32_t fixed = p.xslots * p.xslot_bytes;
-    p.staging_bufs = (fixed + 2 * p.staging_bytes + 6 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
-    if (fixed + p.staging_bufs * p.staging_bytes + 3 * p.stage_bytes > kSmemBudget) strip = false;
-    // small filter banks (64 -> 64) stay resident: no weight traffic after the first tile
+    // small filter banks (64 -> 64, the stem) stay resident: no weight traffic after the first tile
     const uint32_t bank = 9u * p.kc_per_tap * p.stage_bytes;
-    p.b_resident = (strip && p.n_tiles == 1 && fixed + 2 * p.staging_bytes + bank <= kSmemBudget) ? 1 : 0;
-    if (p.b_resident) p.staging_bufs = 2;
+    p.b_resident = (p.n_tiles == 1 && 4 * p.xslot_bytes + 2 * p.staging_bytes + bank <= kSmemBudget) ? 1 : 0;
+    auto fits = [&](int bufs, int xs, int bst) {
+      return (long long)bufs * p.staging_bytes + (long long)xs * p.xslot_bytes +
+             (p.b_resident ? (long long)bank : (long long)bst * p.stage_bytes) <= (long long)kSmemBudget;
+    };
+    p.staging_bufs = fits(2, 6, 6) ? 2 : 1;
+    if (!fits(p.staging_bufs, 4, 3)) {
+      strip = false;
+    } else {
+      int bst = 6;
+      while (!fits(p.staging_bufs, 4, bst)) --bst;         // weight ring: 6 deep if possible, never < 3
+      // every tile needs 3 strips per K chunk and a TMA round trip is ~1.5 us: give the strip ring as
+      // many slots as shared memory allows
+      int xs = 4;
+      while (xs < kMaxXSlots && fits(p.staging_bufs, xs + 1, bst)) ++xs;
+      p.xslots = xs;
+    }
   }
   if (!strip) {
     g = geom_for(N, H, W, 128);
@@ -752,7 +788,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   // pair runs in lock step and the 8 x 8 KB weight ring is too shallow to hide the coupled latency.
   // Kept as an opt-in experiment (profiles/variants_in_situ.txt).
   p.cluster = 1;
-  if (cluster_env() && mode != 2 && mode != 3 && p.m_tiles >= 2 * kNumSMs && (p.block_n % 32 == 0) &&
+  if (kClusterSize == 2 && cluster_env() && mode != 2 && mode != 3 && p.m_tiles >= 2 * kNumSMs && (p.block_n % 32 == 0) &&
       (bmn ? true : (p.block_n / 2) % 8 == 0))
     p.cluster = 2;
   const int unit = p.n_tiles * p.cluster;
@@ -766,8 +802,8 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
   if (strip) {
     long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
-    int box[4] = {64, 130, 1, 1};
-    if (!make_map(&ma, a, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
+    int box[4] = {BK, 130, 1, 1};
+    if (!make_map(&ma, a, 4, dims, str, box, BK * 2)) return (int)cudaErrorInvalidValue;
   } else if (mode != 3) {
     long long dims[4] = {Kc, W, H, N}, str[4] = {1, ld_a, ld_a * W, ld_a * W * H};
     int box[4] = {BK, TW, TH, g.tn};
@@ -804,6 +840,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.xslots * p.xslot_bytes +
                       (size_t)p.staging_bufs * p.staging_bytes + 1024;
   if (strip) {
+    if (BK == 16) return launch_tap<16, false, true>(ma, mb, mo, p, grid, smem, st);
     if (bmn) return launch_tap<64, true, true>(ma, mb, mo, p, grid, smem, st);
     return launch_tap<64, false, true>(ma, mb, mo, p, grid, smem, st);
   }

@@ -19,7 +19,7 @@ PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC_DIR = os.path.join(REPO_DIR, "csrc")
 LIB_DIR = os.path.join(PKG_DIR, "lib")
-LIB_PATH = os.path.join(LIB_DIR, "libb200seg.so")
+LIB_PATH = os.environ.get("B200SEG_LIB") or os.path.join(LIB_DIR, "libb200seg.so")   # B200SEG_LIB: A/B another build
 
 _lib_loaded: Optional[str] = None
 _load_error: Optional[str] = None

@@ -18,6 +18,10 @@ SHAPES = [  # N, H, W, Cin, Cout
     (1, 32, 32, 32, 32),       # reference width 32
     (1, 16, 16, 96, 32),
     (3, 12, 20, 64, 64),       # ragged tiles
+    (1, 6, 256, 64, 64),       # strip mode (rows of 128-pixel segments), resident filter bank
+    (2, 5, 128, 192, 64),      # strip mode, streamed weights, 3 channel chunks
+    (1, 4, 128, 128, 128),     # strip mode, N = 128
+    (1, 8, 128, 16, 64),       # strip mode, stem (K chunk of 16)
 ]
 
 
