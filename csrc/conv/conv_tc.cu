@@ -62,6 +62,7 @@ struct TapGemmParams {
   uint32_t a_bytes, b_bytes, stage_bytes, staging_bytes;
   int staging_bufs;                // 1 or 2 output staging tiles (2: TMA store of tile i overlaps tile i+1)
   int cluster;                     // 1, or 2: CTA pairs (adjacent M tiles) share the weight tile via TMA multicast
+  int rows2;                       // STRIP mode: a work unit is TWO vertically adjacent row tiles sharing every weight tile
   int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
   int xslots;                      // STRIP mode: number of input-strip slots
   uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
@@ -96,7 +97,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   uint8_t* const xring = smem + (size_t)p.stages * p.stage_bytes;     // STRIP: strip slots after the B ring
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_empty[kMaxStages];
   __shared__ __align__(8) uint64_t bar_xfull[kMaxXSlots], bar_xempty[kMaxXSlots];
-  __shared__ __align__(8) uint64_t bar_tfull[2], bar_tempty[2];
+  __shared__ __align__(8) uint64_t bar_tfull[4], bar_tempty[4];
   __shared__ uint32_t tmem_base_s;
   __shared__ float s_bias[256];
 
@@ -125,7 +126,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
     for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], csz); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
+    for (int s = 0; s < 4; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
     for (int s = 0; s < kMaxXSlots; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
     fence_barrier_init();
   }
@@ -176,6 +177,32 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           for (int kc = 0; kc < p.kc_per_tap; ++kc)
             load_b(smem + (size_t)(t * p.kc_per_tap + kc) * p.stage_bytes, &bar_full[0], t, kc);
       }
+      if (p.rows2) {
+        // work unit = output rows (h0, h0+1) of one 128-pixel column segment: 4 input strips per K chunk
+        // (rows h0-1 .. h0+2) and every weight tile ONCE for both rows
+        const int hp_n = p.H >> 1;
+        for (int q = m_first; q < (p.m_tiles >> 1); q += m_step) {
+          const int twi = q % p.tiles_w;
+          const int hp = (q / p.tiles_w) % hp_n;
+          const int n0 = q / (p.tiles_w * hp_n);
+          const int w0 = twi << p.tw_log2, h0 = hp * 2;
+          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+            for (int j = 0; j < 4; ++j) {
+              MBAR_WAIT_OR_TRAP(&bar_xempty[xs], xphase ^ 1);
+              mbar_arrive_expect_tx(&bar_xfull[xs], 130 * KCfg<BLOCK_K>::kRowBytes);
+              tma_load_4d(xring + (size_t)xs * p.xslot_bytes, &map_a, &bar_xfull[xs], kc * BLOCK_K, w0 - 1,
+                          h0 - 1 + j, n0);
+              if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+            }
+            for (int t = 0; t < 9; ++t) {
+              MBAR_WAIT_OR_TRAP(&bar_empty[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&bar_full[stage], p.b_bytes);
+              load_b(smem + (size_t)stage * p.stage_bytes, &bar_full[stage], t, kc);
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      } else
       for (int mu = m_first; mu < m_units; mu += m_step) {
         const int m = min(mu * csz + crank, p.m_tiles - 1);
         const int twi = m % p.tiles_w;
@@ -234,6 +261,58 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       int acc = 0;
       uint32_t acc_phase = 0;
       if (p.b_resident) MBAR_WAIT_OR_TRAP(&bar_full[0], 0);
+      if (p.rows2) {
+        for (int q = m_first; q < (p.m_tiles >> 1); q += m_step) {
+          // accumulator slots acc, acc+1 (of 4, 128 columns each) hold output rows h0 and h0+1
+          MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+          MBAR_WAIT_OR_TRAP(&bar_tempty[acc + 1], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d0 = tmem_base + acc * 128, d1 = d0 + 128;
+          uint32_t first = 0;
+          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+            uint64_t dstrip[4];
+            int xslot[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
+              xslot[j] = xs;
+              dstrip[j] = make_smem_desc(smem_u32(xring + (size_t)xs * p.xslot_bytes), 16, KCfg<BLOCK_K>::kSBO,
+                                         KCfg<BLOCK_K>::kLayout);
+              if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+            }
+            tc_fence_after();
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              const int r = t / 3, sft = t % 3;
+              MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+              tc_fence_after();
+              const int win = (p.flip > 0) ? sft : 2 - sft;
+              // input strip of output row `sub` for filter row r: sub + r (fprop) or sub + 2 - r (dgrad)
+              const int j0 = (p.flip > 0) ? r : 2 - r;
+              const uint64_t a0 = dstrip[j0] + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
+              const uint64_t a1 = dstrip[j0 + 1] + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
+              const uint32_t sb = smem_u32(smem + (size_t)stage * p.stage_bytes);
+              const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
+                                        : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+#pragma unroll
+              for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
+                const uint64_t bk = db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4);
+                umma_bf16(d0, a0 + ((k4 * 32) >> 4), bk, idesc, first);
+                umma_bf16(d1, a1 + ((k4 * 32) >> 4), bk, idesc, first);
+                first = 1u;
+              }
+              release_b(&bar_empty[stage]);
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) umma_commit(&bar_xempty[xslot[j]]);
+          }
+          umma_commit(&bar_tfull[acc]);
+          umma_commit(&bar_tfull[acc + 1]);
+          acc += 2;
+          if (acc == 4) { acc = 0; acc_phase ^= 1; }
+        }
+      } else
       for (int mu = m_first; mu < m_units; mu += m_step) {
         const int m = min(mu * csz + crank, p.m_tiles - 1);
         MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
@@ -344,13 +423,18 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint32_t acc_phase = 0;
     int sbuf = 0;
     uint8_t* const staging0 = staging;
-    for (int mu = m_first; mu < m_units; mu += m_step) {
-      const bool live = mu * csz + crank < p.m_tiles;
+    const int acc_n = p.rows2 ? 4 : 2;                    // accumulator slots in TMEM ...
+    const int acc_cols = p.rows2 ? 128 : 256;             // ... and their column pitch
+    const int subs = p.rows2 ? 2 : 1;
+    const int n_units = p.rows2 ? (p.m_tiles >> 1) : m_units;
+    for (int mu = m_first; mu < n_units; mu += m_step)
+    for (int sub = 0; sub < subs; ++sub) {
+      const bool live = p.rows2 ? true : (mu * csz + crank < p.m_tiles);
       uint8_t* const staging = staging0 + (size_t)sbuf * p.staging_bytes;     // this tile's staging buffer
       if (p.staging_bufs == 2) sbuf ^= 1;
       MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + acc * 256 + (static_cast<uint32_t>(rb * 32) << 16);
+      const uint32_t t_addr = tmem_base + acc * acc_cols + (static_cast<uint32_t>(rb * 32) << 16);
       for (int c0 = colhalf * 32; c0 < block_n; c0 += 64) {
         uint32_t r[32];
         const bool wide = block_n - c0 >= 32;
@@ -385,16 +469,23 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       }
       tc_fence_before();
       mbar_arrive(&bar_tempty[acc]);                      // accumulator drained: MMA may reuse it
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
       fence_proxy_async();                                // staging writes -> visible to TMA
       named_bar_sync(1, kEpiThreads);
       int w0 = 0, h0 = 0, n0 = 0;
       if (et == 0 || (ragged && want_stats)) {            // tile coordinates: integer divisions, off the hot path
-        const int m = min(mu * csz + crank, p.m_tiles - 1);
-        const int twi = m % p.tiles_w;
-        const int thi = (m / p.tiles_w) % p.tiles_h;
-        const int g_img = m / (p.tiles_w * p.tiles_h);
-        w0 = twi << p.tw_log2; h0 = thi << p.th_log2; n0 = g_img * p.tn;
+        if (p.rows2) {
+          const int hp_n = p.H >> 1;
+          w0 = (mu % p.tiles_w) << p.tw_log2;
+          h0 = ((mu / p.tiles_w) % hp_n) * 2 + sub;
+          n0 = mu / (p.tiles_w * hp_n);
+        } else {
+          const int m = min(mu * csz + crank, p.m_tiles - 1);
+          const int twi = m % p.tiles_w;
+          const int thi = (m / p.tiles_w) % p.tiles_h;
+          const int g_img = m / (p.tiles_w * p.tiles_h);
+          w0 = twi << p.tw_log2; h0 = thi << p.th_log2; n0 = g_img * p.tn;
+        }
       }
       if (want_stats && live) {
         const uint8_t* gb = staging + st_grp * group_bytes;
@@ -695,6 +786,12 @@ static int cluster_env() {             // B200SEG_CLUSTER=1 enables CTA-pair wei
   return v;
 }
 
+static int rows2_env() {               // B200SEG_ROWS2=0 disables the two-row strip work units
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_ROWS2"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return v;
+}
+
 static int strip_mode_env() {          // B200SEG_CONV_STRIP=0 disables the strip path (benchmarking)
   static int v = -1;
   if (v < 0) { const char* e = getenv("B200SEG_CONV_STRIP"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
@@ -756,6 +853,11 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
              (p.b_resident ? (long long)bank : (long long)bst * p.stage_bytes) <= (long long)kSmemBudget;
     };
     p.staging_bufs = fits(2, 6, 6) ? 2 : 1;
+    // two-row work units (every weight tile serves two output rows) when the filter bank is streamed:
+    // needs an even height, N <= 128 (four 128-column accumulators) and room for 8 strips
+    p.rows2 = (!p.b_resident && rows2_env() && (H % 2 == 0) && p.block_n <= 128 &&
+               fits(1, 8, 3)) ? 1 : 0;
+    if (p.rows2) p.staging_bufs = fits(2, 8, 6) ? 2 : 1;
     if (!fits(p.staging_bufs, 4, 3)) {
       strip = false;
     } else {
@@ -763,8 +865,10 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
       while (!fits(p.staging_bufs, 4, bst)) --bst;         // weight ring: 6 deep if possible, never < 3
       // every tile needs 3 strips per K chunk and a TMA round trip is ~1.5 us: give the strip ring as
       // many slots as shared memory allows
-      int xs = 4;
+      int xs = p.rows2 ? 8 : 4;
+      while (!fits(p.staging_bufs, xs, bst) && bst > 3) --bst;
       while (xs < kMaxXSlots && fits(p.staging_bufs, xs + 1, bst)) ++xs;
+      if (p.rows2) xs -= xs % 4;                            // a K chunk's four strips never straddle the ring end
       p.xslots = xs;
     }
   }
@@ -773,7 +877,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
     p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
     p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
-    p.xslots = 0; p.xslot_bytes = 0;
+    p.xslots = 0; p.xslot_bytes = 0; p.rows2 = 0; p.b_resident = 0;
     p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
     p.staging_bufs = (2 * p.staging_bytes + 4 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
   }
@@ -793,7 +897,8 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.cluster = 2;
   const int unit = p.n_tiles * p.cluster;
   int grid = kNumSMs - (kNumSMs % unit);
-  const long long total = (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
+  const long long total = p.rows2 ? (long long)(p.m_tiles / 2) * unit
+                                  : (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
   if (total < grid) grid = (int)total;
   if (stat_rows_out) *stat_rows_out = grid / p.n_tiles;
   if (dry) return 0;

@@ -22,6 +22,7 @@ SHAPES = [  # N, H, W, Cin, Cout
     (2, 5, 128, 192, 64),      # strip mode, streamed weights, 3 channel chunks
     (1, 4, 128, 128, 128),     # strip mode, N = 128
     (1, 8, 128, 16, 64),       # strip mode, stem (K chunk of 16)
+    (2, 6, 256, 128, 64),      # strip mode, two-row work units (streamed weights, even height)
 ]
 
 
