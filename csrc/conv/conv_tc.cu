@@ -584,6 +584,7 @@ struct WgradParams {
   int nt_per_q;                             // convT: N tiles per quadrant
   int H;                                    // convT: low-res height (Y = n*H + y)
   long long co_stride;                      // floats between consecutive output channels in dw
+  int tap0;                                 // first filter tap handled (m_blocks counts taps from here)
 };
 
 __global__ void __launch_bounds__(kConvThreads, 1)
@@ -636,7 +637,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
           for (int hb = 0; hb < 2 * p.mt; ++hb) {
             int blk = m_tile * 2 * p.mt + hb;
             if (blk >= p.m_blocks) blk = p.m_blocks - 1;     // padding block: loaded, never stored
-            const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
+            const int t = p.tap0 + blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
             const int dw_ = p.convt ? 0 : (t % 3 - 1), dh_ = p.convt ? 0 : (t / 3 - 1);
             tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0);
           }
@@ -687,7 +688,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
         int blk = (m_tile * p.mt + mt) * 2 + (row >> 6);
         const bool blk_ok = blk < p.m_blocks;
         if (!blk_ok) blk = p.m_blocks - 1;
-        const int t = blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
+        const int t = p.tap0 + blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
         const int ci = cc * 64 + (row & 63);
         const bool row_ok = blk_ok && ci < p.Cin;
         const uint32_t t_addr = tmem_base + mt * 256 + (static_cast<uint32_t>(rb * 32) << 16);
@@ -989,7 +990,7 @@ extern "C" int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, 
 }
 
 static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
-                     int H, int W, int Cin, int Cout, cudaStream_t st) {
+                     int H, int W, int Cin, int Cout, cudaStream_t st, int tap0 = 0, int ntaps = 9) {
   if (Cin % 8 || Cout % 16) return (int)cudaErrorInvalidValue;
   WgradParams p{};
   TileGeom g = geom_for(N, H, W, 64);
@@ -999,7 +1000,8 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
   p.Cin = Cin; p.Cout = Cout;
   p.chunks_per_tap = (Cin + 63) / 64;
-  p.m_blocks = (convt ? 1 : 9) * p.chunks_per_tap;
+  p.m_blocks = (convt ? 1 : ntaps) * p.chunks_per_tap;
+  p.tap0 = convt ? 0 : tap0;
   // Two 128-row M tiles per CTA share each dy tile (halves the dy traffic per FLOP).  In isolation it is
   // neutral, inside the training step it is worth 1.5 ms of 35 (profiles/variants_in_situ.txt), so it
   // is the default; B200SEG_WGRAD_MT=1 turns it off.
@@ -1060,6 +1062,13 @@ extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int 
 extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout);
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
                                     int N, int H, int W, int Cin, int Cout, cudaStream_t st);
+
+// One filter tap (or a range) with the split-K kernel: the 128-column strip kernel leaves tap (2,2) to it.
+extern "C" int b200conv_wgrad_taps(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                                   int H, int W, int Cin, int Cout, int tap0, int ntaps, cudaStream_t st) {
+  if (tap0 < 0 || ntaps < 1 || tap0 + ntaps > 9) return (int)cudaErrorInvalidValue;
+  return run_wgrad(0, x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st, tap0, ntaps);
+}
 
 // Dispatch: halo-strip kernel (wgrad_strip.cu) when the rows are at least 64 pixels wide, else the
 // split-K kernel above.  B200SEG_WGRAD_KERNEL=splitk|strip forces one of them (for benchmarking).

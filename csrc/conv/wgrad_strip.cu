@@ -12,13 +12,24 @@
 //   * all nine taps are UMMA operands that point INTO those strips: tap (r,s) is the window of 64
 //     pixel-rows starting s rows into strip r.  tcgen05 applies the 128-byte swizzle as a function
 //     of the absolute shared-memory address, so a window that starts on any 128-byte row is a valid
-//     MN-major operand (probed on hardware, csrc/standalone_umma_probe.cu exp 5).  Two taps of the
-//     same strip form one M = 128 tile (leading byte offset = one row = 128 B); per filter row that
-//     is {(r,0),(r,1)} and {(r,2), unused}: six accumulators of 64 columns in TMEM (384 of 512).
+//     MN-major operand (probed on hardware, csrc/standalone_umma_probe.cu exp 5).  Two taps form one
+//     M = 128 tile; the descriptor's leading byte offset is the distance between them:
+//         tiles 0..2 : {(r,0),(r,1)}   same strip, one row apart (LBO = 128 B)
+//         tile  3    : {(0,2),(1,2)}   consecutive strips (LBO = one ring stage)
+//         tile  4    : {(2,2), unused} (64-column variant only)
+//     Tile 3 needs strip r+1 exactly one stage after strip r, which fails where the ring wraps; so
+//     whatever is loaded into slot 0 is ALSO loaded into a mirror slot after the last one (1/8 more
+//     strip traffic) and slot 7 + one stage is always the right partner.
+//   * BN = 64 output channels per CTA: five accumulators of 64 columns, all nine taps (9/10 of the
+//     issued MMA rows are useful; with N = 64 the MMA is shared-memory-bound at 2/3 of peak).
+//     BN = 128 (Cout % 128 == 0): four accumulators of 128 columns = all of TMEM, taps 0..7 at the
+//     full tensor-core rate with no padding; tap (2,2) is left to the split-K kernel (1/9 of the work).
 //   * the accumulators persist across all the pixels the CTA visits; the epilogue runs once and adds
 //     the 9 x 64 x 64 block into the fp32 gradient buffer with red.global.add (the buffer accumulates
 //     over micro-batches anyway, R:756).
 // Out-of-image strips (row -1, row H, the halo columns) are zero-filled by TMA = the conv padding.
+#include <cstdlib>
+
 #include "umma.cuh"
 #include "../common.cuh"
 #include "b200seg.h"
@@ -29,17 +40,22 @@ namespace b200 {
 constexpr int kWsThreads = 192;
 constexpr int kWsStages = 8;
 constexpr uint32_t kStripBytes = 9216;       // 66 rows x 128 B = 8448, padded to 9 KiB (72 rows)
-constexpr uint32_t kDyBytes = 8192;          // 64 pixels x 64 channels
-constexpr uint32_t kWsStageBytes = kStripBytes + kDyBytes;
+template <int BN> struct WsCfg {
+  static constexpr int kTiles = BN == 64 ? 5 : 4;
+  static constexpr uint32_t kDyBytes = BN * 128;               // 64 pixels x BN channels
+  static constexpr uint32_t kStageBytes = kStripBytes + kDyBytes;
+  static constexpr size_t kSmem = (size_t)kWsStages * kStageBytes + kStripBytes + 1024;   // + mirror slot
+};
 
 struct WgradStripParams {
   int N, H, W, Cin, Cout;
-  int chunks, n_tiles, groups;         // Cin/64 (rounded up), Cout/64 (rounded up), chunks * n_tiles
+  int chunks, n_tiles, groups;         // Cin/64 (rounded up), Cout/BN (rounded up), chunks * n_tiles
   int ctas_per_group;
   int wsegs, rows_per_piece, pieces_per_col, pieces;   // pieces per group
   float* dw;
 };
 
+template <int BN>
 __global__ void __launch_bounds__(kWsThreads, 1)
 wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
                    const WgradStripParams p) {
@@ -49,6 +65,8 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   __shared__ __align__(8) uint64_t bar_done;
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr uint32_t kDyBytes = WsCfg<BN>::kDyBytes, kWsStageBytes = WsCfg<BN>::kStageBytes;
+  constexpr int kTiles = WsCfg<BN>::kTiles;
 
   const int group = blockIdx.x % p.groups;
   const int member = blockIdx.x / p.groups;              // which CTA of the group
@@ -86,16 +104,26 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           MBAR_WAIT_OR_TRAP(&bar_empty[st], ((q / kWsStages) & 1) ^ 1);
           uint8_t* sx = smem + (size_t)st * kWsStageBytes;
           const bool with_dy = j >= 2;
-          mbar_arrive_expect_tx(&bar_full[st], 66 * 128 + (with_dy ? kDyBytes : 0));
+          const bool mirror = st == 0;                     // slot 0 is duplicated behind the last slot
+          mbar_arrive_expect_tx(&bar_full[st], (mirror ? 2 : 1) * 66 * 128 + (with_dy ? kDyBytes : 0));
           tma_load_4d(sx, &map_x, &bar_full[st], chunk * 64, w0 - 1, h0 - 1 + j, n);
-          if (with_dy) tma_load_4d(sx + kStripBytes, &map_dy, &bar_full[st], n_tile * 64, w0, h0 + j - 2, n);
+          if (mirror)
+            tma_load_4d(smem + (size_t)kWsStages * kWsStageBytes, &map_x, &bar_full[st], chunk * 64, w0 - 1,
+                        h0 - 1 + j, n);
+          if (with_dy) {
+#pragma unroll
+            for (int nb = 0; nb < BN / 64; ++nb)
+              tma_load_4d(sx + kStripBytes + nb * 8192, &map_dy, &bar_full[st], n_tile * BN + nb * 64, w0,
+                          h0 + j - 2, n);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer ----------------------------------
     if (elect_one() && has_work) {
-      const uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+      const uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
+      const uint32_t sbase = smem_u32(smem);
       uint32_t q = 0;
       bool first = true;
       for (int piece = member; piece < p.pieces; piece += p.ctas_per_group) {
@@ -108,22 +136,21 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           MBAR_WAIT_OR_TRAP(&bar_full[st], (q / kWsStages) & 1);
           if (j < 2) continue;                              // halo rows of the piece: loaded only
           tc_fence_after();
-          // descriptors: build once per operand base, then only bump the 14-bit address field
-          const uint64_t db0 = make_smem_desc(smem_u32(smem + (size_t)st * kWsStageBytes + kStripBytes), 8192, 1024,
-                                              LAYOUT_SW128);
+          const uint32_t strip0 = sbase + ((q - 2) % kWsStages) * kWsStageBytes;   // filter row 0
+          const uint32_t strip1 = sbase + ((q - 1) % kWsStages) * kWsStageBytes;
+          const uint32_t strip2 = sbase + st * kWsStageBytes;
+          const uint64_t db0 = make_smem_desc(strip2 + kStripBytes, 8192, 1024, LAYOUT_SW128);
           const uint32_t acc0 = first ? 0u : 1u;
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {
-            const uint64_t da0 = make_smem_desc(
-                smem_u32(smem + (size_t)((q - 2 + r) % kWsStages) * kWsStageBytes), 128, 1024, LAYOUT_SW128);
+          for (int t = 0; t < kTiles; ++t) {
+            uint64_t da0;
+            if (t < 3) da0 = make_smem_desc(t == 0 ? strip0 : (t == 1 ? strip1 : strip2), 128, 1024, LAYOUT_SW128);
+            else if (t == 3) da0 = make_smem_desc(strip0 + 256, kWsStageBytes, 1024, LAYOUT_SW128);   // + mirror
+            else da0 = make_smem_desc(strip2 + 256, 128, 1024, LAYOUT_SW128);
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {          // {(r,0),(r,1)} and {(r,2), unused}
-              const uint32_t d_tmem = tmem_base + (r * 2 + half) * 64;
-#pragma unroll
-              for (int k4 = 0; k4 < 4; ++k4)
-                umma_bf16(d_tmem, da0 + ((half * 256 + k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
-                          k4 == 0 ? acc0 : 1u);
-            }
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_bf16(tmem_base + t * BN, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
+                        k4 == 0 ? acc0 : 1u);
           }
           first = false;
           umma_commit(&bar_empty[(q - 2) % kWsStages]);    // oldest strip is no longer needed
@@ -144,21 +171,22 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     tc_fence_after();
     const size_t co_stride = (size_t)9 * p.Cin;
 #pragma unroll 1
-    for (int acc = 0; acc < 6; ++acc) {
-      const int r = acc >> 1, half = acc & 1;
-      const int s = half * 2 + (row >> 6);                  // tap column: 0,1 | 2,(3 = unused)
-      if (s > 2) continue;                                  // warp-uniform (row >> 6 is per warp pair)
+    for (int t = 0; t < kTiles; ++t) {
+      const int hi = row >> 6;                              // which tap of the tile (warp-uniform)
+      const int r = t < 3 ? t : (t == 3 ? hi : 2);
+      const int s = t < 3 ? hi : 2;
+      if (t == 4 && hi) continue;                           // padding half of the last tile
       const bool row_ok = ci < p.Cin;
       float* base = p.dw + (size_t)(r * 3 + s) * p.Cin + ci;
-      const uint32_t t_addr = tmem_base + acc * 64 + (static_cast<uint32_t>(rb * 32) << 16);
-#pragma unroll
-      for (int c0 = 0; c0 < 64; c0 += 32) {
+      const uint32_t t_addr = tmem_base + t * BN + (static_cast<uint32_t>(rb * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
         tmem_ld_32x32b_x32(t_addr + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const int co = n_tile * 64 + c0 + j;
+          const int co = n_tile * BN + c0 + j;
           if (row_ok && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(v[j]));
         }
       }
@@ -173,25 +201,48 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 
 using namespace b200;
 
-// Supported whenever a row holds at least one 64-pixel strip.  `preferred` additionally encodes the
-// measured crossover: with 64-column accumulators the UMMA is shared-memory-bound (67 % of peak) and
-// one tile in four is padding, so for Cout > 128 (layers that are not L2-bound anyway) the split-K
-// kernel with 256-column tiles is faster (profiles/conv_layers_*.txt).
+// Supported whenever a row holds at least one 64-pixel strip.  `preferred`: rows narrower than 64
+// pixels (and channel counts the split-K kernel tiles better) stay on the split-K kernel.
+// B200SEG_WGRAD_BN=64 forces the 64-column variant (A/B runs).
 extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout) {
   (void)N; (void)H;
   return (W >= 64 && Cin % 8 == 0 && Cout % 8 == 0) ? 1 : 0;
 }
+static int strip_bn(int Cout) {
+  static int force64 = -1;
+  if (force64 < 0) { const char* e = getenv("B200SEG_WGRAD_BN"); force64 = (e != nullptr && e[0] == '6') ? 1 : 0; }
+  return (!force64 && Cout % 128 == 0) ? 128 : 64;
+}
 extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout) {
-  return (b200conv_wgrad_strip_supported(N, H, W, Cin, Cout) && Cout <= 128) ? 1 : 0;
+  if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return 0;
+  return (Cout <= 128 || strip_bn(Cout) == 128) ? 1 : 0;
+}
+
+extern "C" int b200conv_wgrad_taps(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                                   int H, int W, int Cin, int Cout, int tap0, int ntaps, cudaStream_t st);
+
+template <int BN>
+static int launch_strip(const CUtensorMap& mx, const CUtensorMap& mdy, const WgradStripParams& p, int grid,
+                        cudaStream_t st) {
+  static bool attr_done = false;
+  const size_t smem = WsCfg<BN>::kSmem;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_strip_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  wgrad_strip_kernel<BN><<<grid, kWsThreads, smem, st>>>(mx, mdy, p);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
                                     int N, int H, int W, int Cin, int Cout, cudaStream_t st) {
   if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return (int)cudaErrorInvalidValue;
+  const int bn = strip_bn(Cout);
   WgradStripParams p{};
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
   p.chunks = (Cin + 63) / 64;
-  p.n_tiles = (Cout + 63) / 64;
+  p.n_tiles = (Cout + bn - 1) / bn;
   p.groups = p.chunks * p.n_tiles;
   p.wsegs = (W + 63) / 64;
   p.rows_per_piece = H < 32 ? H : 32;
@@ -213,13 +264,8 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
     int box[4] = {64, 64, 1, 1};
     if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   }
-  static bool attr_done = false;
-  const size_t smem = (size_t)kWsStages * kWsStageBytes + 1024;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    attr_done = true;
-  }
-  wgrad_strip_kernel<<<p.groups * cpg, kWsThreads, smem, st>>>(mx, mdy, p);
-  return (int)cudaGetLastError();
+  if (bn == 64) return launch_strip<64>(mx, mdy, p, p.groups * cpg, st);
+  int rc = launch_strip<128>(mx, mdy, p, p.groups * cpg, st);
+  if (rc != 0) return rc;
+  return b200conv_wgrad_taps(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, 8, 1, st);   // tap (2,2)
 }

@@ -112,6 +112,9 @@ int b200conv_dgrad(const void* dy, long long ld_dy, const void* w, void* dx, lon
                    int H, int W, int Cin, int Cout, cudaStream_t st);
 int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
                    int H, int W, int Cin, int Cout, cudaStream_t st);
+/* the same for filter taps tap0 .. tap0+ntaps-1 only (tap = 3*r + s), split-K kernel */
+int b200conv_wgrad_taps(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                        int H, int W, int Cin, int Cout, int tap0, int ntaps, cudaStream_t st);
 int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, const float* bias, void* out,
                        long long ld_o, int N, int h, int w_, int Cin, int Cout, cudaStream_t st);
 /* backward of the transposed conv: d_up (N,2h,2w,Cout) slice; w, dw laid out [(dy,dx,co)][ci] */

@@ -23,6 +23,8 @@ SHAPES = [  # N, H, W, Cin, Cout
     (1, 4, 128, 128, 128),     # strip mode, N = 128
     (1, 8, 128, 16, 64),       # strip mode, stem (K chunk of 16)
     (2, 6, 256, 128, 64),      # strip mode, two-row work units (streamed weights, even height)
+    (1, 40, 64, 192, 64),      # wgrad strip ring wraps (mirror slot), two pieces per column
+    (2, 40, 128, 64, 256),     # wgrad strip, 128-column variant + tap (2,2) on the split-K kernel
 ]
 
 
