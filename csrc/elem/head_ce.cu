@@ -12,6 +12,7 @@
 #include "../common.cuh"
 #include "b200seg.h"
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace b200 {
@@ -211,6 +212,281 @@ head_ce_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float*
   if (threadIdx.x == 0) *counter = 0u;               // ready for the next launch
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// Fast path for the shapes the U-Net actually has (C = 32 / 64 / 128 channels, K <= 8 classes).
+// Same arithmetic as head_ce_kernel (bit-identical logits, predictions and da), reorganised around
+// what bounds the generic kernel: shared-memory read bandwidth.  A warp-wide 16-byte load costs
+// four cycles of the SM's 128 B/clk path even when every lane reads the same address, and the
+// generic kernel issues two such broadcast loads of weights per eight FMAs.  Here
+//   * a warp owns a tile of 128 pixels and every lane four of them (64 and two for C = 128), so each
+//     weight vector fetched from shared memory feeds 32 FMAs instead of 8;
+//   * the dW phase maps a lane to (8 channels, a subset of the pixels): it reads distinct 16-byte
+//     pieces of the activation tile (no broadcast) and does K*8 FMAs per load; the pixel subsets are
+//     folded with shuffles once, at the end of the kernel;
+//   * loops are unrolled over compile-time K and C, and the da tile overwrites the activation tile.
+constexpr int kHfWarps = 8;
+template <int CT> struct HfCfg {
+  static constexpr int kPix = CT > 64 ? 2 : 4;                  // pixels per lane (shared memory bounds it)
+  static constexpr int kTile = 32 * kPix;                       // pixels per warp tile
+};
+
+template <int KT, int CT>
+__global__ void __launch_bounds__(kHfWarps * 32, 1)
+head_ce_fast_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const float* __restrict__ w,
+                    const float* __restrict__ bias, const uint8_t* __restrict__ labels, long long P, int K,
+                    float grad_scale, __nv_bfloat16* __restrict__ da, long long ld_da, float* __restrict__ dw,
+                    float* __restrict__ db, uint8_t* __restrict__ pred, float* __restrict__ loss_acc,
+                    float* __restrict__ workspace, unsigned int* __restrict__ counter) {
+  extern __shared__ __align__(16) uint8_t smraw[];
+  constexpr int kHfPix = HfCfg<CT>::kPix, kHfTile = HfCfg<CT>::kTile;
+  constexpr int pitch = CT + 8;                               // bf16 elements per tile row
+  constexpr int CV = CT / 8;                                  // 16-byte pieces per pixel
+  constexpr int NSUB = 32 / CV;                               // pixel subsets in the dW phase
+  const int nred = K * CT + K + 2;
+  float* s_w = reinterpret_cast<float*>(smraw);               // [KT][CT], rows >= K are zero
+  float* s_b = s_w + KT * CT;                                 // [8]
+  float* s_red = s_b + 8;                                     // [nred]
+  float* s_dl = s_red + ((nred + 3) & ~3);                    // [warps][tile][8]
+  __nv_bfloat16* s_tiles = reinterpret_cast<__nv_bfloat16*>(s_dl + kHfWarps * kHfTile * 8);   // [warps][tile][pitch]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < KT * CT; i += blockDim.x) s_w[i] = i < K * CT ? w[i] : 0.f;
+  for (int i = threadIdx.x; i < 8; i += blockDim.x) s_b[i] = i < K ? bias[i] : 0.f;
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+
+  const bool bwd = (da != nullptr);
+  __nv_bfloat16* t_a = s_tiles + (size_t)warp * kHfTile * pitch;
+  float* my_dl = s_dl + warp * kHfTile * 8;
+  const int cvl = lane % CV, sub = lane / CV;                 // dW phase: channel piece, pixel subset
+  float accw[KT][8];
+  float accb[KT];
+#pragma unroll
+  for (int k = 0; k < KT; ++k) {
+    accb[k] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) accw[k][j] = 0.f;
+  }
+  float loss_local = 0.f, correct_local = 0.f;
+
+  const long long chunks = (P + kHfTile - 1) / kHfTile;
+  for (long long ch = (long long)blockIdx.x * kHfWarps + warp; ch < chunks; ch += (long long)gridDim.x * kHfWarps) {
+    const long long p0 = ch * kHfTile;
+    // 1. coalesced tile load
+#pragma unroll 8
+    for (int i0 = 0; i0 < kHfTile * CV; i0 += 32) {
+      const int i = i0 + lane;
+      const int px = i / CV, cv = i - px * CV;
+      bf16x8 v;
+      if (p0 + px < P) v = ld8(a + (p0 + px) * ld_a + cv * 8);
+      else { v.v[0] = v.v[1] = v.v[2] = v.v[3] = __floats2bfloat162_rn(0.f, 0.f); }
+      *reinterpret_cast<bf16x8*>(t_a + px * pitch + cv * 8) = v;
+    }
+    __syncwarp();
+    // 2. logits (lane = four pixels: lane, lane + 32, ...)
+    float z[kHfPix][KT];
+#pragma unroll
+    for (int q = 0; q < kHfPix; ++q)
+#pragma unroll
+      for (int k = 0; k < KT; ++k) z[q][k] = s_b[k];
+#pragma unroll
+    for (int cv = 0; cv < CV; ++cv) {
+      float f[kHfPix][8];
+#pragma unroll
+      for (int q = 0; q < kHfPix; ++q)
+        unpack8(*reinterpret_cast<const bf16x8*>(t_a + (q * 32 + lane) * pitch + cv * 8), f[q]);
+#pragma unroll
+      for (int k = 0; k < KT; ++k) {
+        const float4 w0 = *reinterpret_cast<const float4*>(s_w + k * CT + cv * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(s_w + k * CT + cv * 8 + 4);
+#pragma unroll
+        for (int q = 0; q < kHfPix; ++q) {
+          float t = z[q][k];
+          t = fmaf(f[q][0], w0.x, fmaf(f[q][1], w0.y, fmaf(f[q][2], w0.z, fmaf(f[q][3], w0.w, t))));
+          t = fmaf(f[q][4], w1.x, fmaf(f[q][5], w1.y, fmaf(f[q][6], w1.z, fmaf(f[q][7], w1.w, t))));
+          z[q][k] = t;
+        }
+      }
+    }
+    // 3. softmax, loss, arg-max; dl -> registers and the staging tile
+    float dl[kHfPix][KT];
+#pragma unroll
+    for (int q = 0; q < kHfPix; ++q) {
+      const long long p = p0 + q * 32 + lane;
+      const bool valid = p < P;
+#pragma unroll
+      for (int k = 0; k < KT; ++k) z[q][k] = (k < K) ? z[q][k] : -INFINITY;
+      float mx = z[q][0];
+      int arg = 0;
+#pragma unroll
+      for (int k = 1; k < KT; ++k)
+        if (z[q][k] > mx) { mx = z[q][k]; arg = k; }
+      float e[KT], sum = 0.f;
+#pragma unroll
+      for (int k = 0; k < KT; ++k) { e[k] = (k < K) ? __expf(z[q][k] - mx) : 0.f; sum += e[k]; }
+      const int lab = valid ? (int)labels[p] : 0;
+      if (valid) {
+        float zl = 0.f;
+#pragma unroll
+        for (int k = 0; k < KT; ++k) zl = (k == lab) ? z[q][k] : zl;
+        loss_local += __logf(sum) + mx - zl;
+        correct_local += (arg == lab) ? 1.f : 0.f;
+        if (pred != nullptr) pred[p] = (uint8_t)arg;
+      }
+      const float inv = grad_scale / sum;
+      float d8[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d8[k] = 0.f;
+#pragma unroll
+      for (int k = 0; k < KT; ++k) {
+        dl[q][k] = (valid && k < K) ? (e[k] * inv - ((k == lab) ? grad_scale : 0.f)) : 0.f;
+        d8[k] = dl[q][k];
+        accb[k] += dl[q][k];
+      }
+      if (bwd) {
+        float4* dst = reinterpret_cast<float4*>(my_dl + (q * 32 + lane) * 8);
+        dst[0] = make_float4(d8[0], d8[1], d8[2], d8[3]);
+        dst[1] = make_float4(d8[4], d8[5], d8[6], d8[7]);
+      }
+    }
+    if (bwd) {
+      __syncwarp();
+      // 4. dW: lane = (channel piece cvl, pixel subset sub); distinct 16-byte reads of the tile
+#pragma unroll 4
+      for (int i = 0; i < kHfTile / NSUB; ++i) {
+        const int px = i * NSUB + sub;
+        float av[8];
+        unpack8(*reinterpret_cast<const bf16x8*>(t_a + px * pitch + cvl * 8), av);
+        float dv[8];
+        *reinterpret_cast<float4*>(dv) = *reinterpret_cast<const float4*>(my_dl + px * 8);
+        if (KT > 4) *reinterpret_cast<float4*>(dv + 4) = *reinterpret_cast<const float4*>(my_dl + px * 8 + 4);
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) accw[k][j] = fmaf(dv[k], av[j], accw[k][j]);
+        }
+      }
+      __syncwarp();
+      // 5. da rows overwrite the activation tile (lane = pixel again)
+#pragma unroll
+      for (int cv = 0; cv < CV; ++cv) {
+        float o[kHfPix][8];
+#pragma unroll
+        for (int q = 0; q < kHfPix; ++q)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[q][j] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+          const float4 w0 = *reinterpret_cast<const float4*>(s_w + k * CT + cv * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(s_w + k * CT + cv * 8 + 4);
+#pragma unroll
+          for (int q = 0; q < kHfPix; ++q) {
+            const float d = dl[q][k];
+            o[q][0] = fmaf(d, w0.x, o[q][0]); o[q][1] = fmaf(d, w0.y, o[q][1]);
+            o[q][2] = fmaf(d, w0.z, o[q][2]); o[q][3] = fmaf(d, w0.w, o[q][3]);
+            o[q][4] = fmaf(d, w1.x, o[q][4]); o[q][5] = fmaf(d, w1.y, o[q][5]);
+            o[q][6] = fmaf(d, w1.z, o[q][6]); o[q][7] = fmaf(d, w1.w, o[q][7]);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < kHfPix; ++q)
+          *reinterpret_cast<bf16x8*>(t_a + (q * 32 + lane) * pitch + cv * 8) = pack8(o[q]);
+      }
+      __syncwarp();
+      // 6. coalesced tile store
+#pragma unroll 8
+      for (int i0 = 0; i0 < kHfTile * CV; i0 += 32) {
+        const int i = i0 + lane;
+        const int px = i / CV, cv = i - px * CV;
+        if (p0 + px < P)
+          st8(da + (p0 + px) * ld_da + cv * 8, *reinterpret_cast<const bf16x8*>(t_a + px * pitch + cv * 8));
+      }
+    }
+    __syncwarp();
+  }
+  // ---- block reduction -> per-CTA partial -----------------------------------------------------
+  loss_local = warp_sum(loss_local);
+  correct_local = warp_sum(correct_local);
+#pragma unroll
+  for (int k = 0; k < KT; ++k) {
+    accb[k] = warp_sum(accb[k]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+      for (int o = CV; o < 32; o <<= 1) accw[k][j] += __shfl_xor_sync(0xffffffffu, accw[k][j], o);
+    }
+  }
+  for (int wv = 0; wv < kHfWarps; ++wv) {               // fixed warp order: deterministic sums
+    if (warp == wv) {
+      if (bwd) {
+#pragma unroll
+        for (int k = 0; k < KT; ++k)
+          if (k < K) {
+            if (lane < CV) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) s_red[k * CT + lane * 8 + j] += accw[k][j];
+            }
+            if (lane == 0) s_red[K * CT + k] += accb[k];
+          }
+      }
+      if (lane == 0) {
+        s_red[K * CT + K] += loss_local;
+        s_red[K * CT + K + 1] += correct_local;
+      }
+    }
+    __syncthreads();
+  }
+  float* mine = workspace + (size_t)blockIdx.x * nred;
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) mine[i] = s_red[i];
+  __threadfence();
+  __shared__ unsigned int s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < nred; i += blockDim.x) {
+    float t = 0.f;
+    for (unsigned int b = 0; b < gridDim.x; ++b) t += workspace[(size_t)b * nred + i];
+    if (i < K * CT) { if (bwd) dw[i] += t; }
+    else if (i < K * CT + K) { if (bwd) db[i - K * CT] += t; }
+    else loss_acc[i - K * CT - K] = t;
+  }
+  if (threadIdx.x == 0) *counter = 0u;
+}
+
+template <int KT, int CT>
+static int launch_head_fast(const void* a, long long ld_a, const float* w, const float* bias,
+                            const unsigned char* labels, long long P, int K, float grad_scale, void* da,
+                            long long ld_da, float* dw, float* db, unsigned char* pred, float* loss_acc, float* ws,
+                            unsigned int* counter, cudaStream_t st) {
+  constexpr int kHfTile = HfCfg<CT>::kTile;
+  const long long chunks = (P + kHfTile - 1) / kHfTile;
+  int grid = (int)((chunks + kHfWarps - 1) / kHfWarps);
+  if (grid > kNumSMs) grid = kNumSMs;
+  if (grid < 1) grid = 1;
+  const int nred_max = 8 * CT + 8 + 2;
+  const size_t smem = sizeof(float) * ((size_t)KT * CT + 8 + ((nred_max + 3) & ~3) + (size_t)kHfWarps * kHfTile * 8) +
+                      (size_t)kHfWarps * kHfTile * (CT + 8) * 2;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(head_ce_fast_kernel<KT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  head_ce_fast_kernel<KT, CT><<<grid, kHfWarps * 32, smem, st>>>(
+      (const __nv_bfloat16*)a, ld_a, w, bias, labels, P, K, grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred,
+      loss_acc, ws, counter);
+  return (int)cudaGetLastError();
+}
+
+static int head_fast_env() {           // B200SEG_HEAD_FAST=0 keeps the generic kernel (A/B runs)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_HEAD_FAST"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return v;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -238,6 +514,20 @@ extern "C" int b200seg_head_ce(const void* a, long long ld_a, const float* w, co
                 (size_t)warps * 2 * 32 * (C + 8) * 2;
   float* ws = (float*)workspace;
   unsigned int* counter = (unsigned int*)((char*)workspace + b200seg_head_ce_workspace_bytes(C, K) - 256);
+  if (K <= 8 && (C == 32 || C == 64 || C == 128) && head_fast_env()) {
+#define B200_HEAD_FAST(KT, CT)                                                                                  \
+  return launch_head_fast<KT, CT>(a, ld_a, w, bias, labels, P, K, grad_scale, da, ld_da, dw, db, pred, loss_acc, \
+                                  ws, counter, st)
+    if (K <= 6) {
+      if (C == 32) B200_HEAD_FAST(6, 32);
+      if (C == 64) B200_HEAD_FAST(6, 64);
+      B200_HEAD_FAST(6, 128);
+    }
+    if (C == 32) B200_HEAD_FAST(8, 32);
+    if (C == 64) B200_HEAD_FAST(8, 64);
+    B200_HEAD_FAST(8, 128);
+#undef B200_HEAD_FAST
+  }
   cudaError_t e;
   if (KMAX == 8) {
     e = cudaFuncSetAttribute(head_ce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -75,7 +75,7 @@ def test_bn_relu_pool_bwd(C, pool, with_dout):
     torch.testing.assert_close(dy.cpu().float(), dy_r, rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("C,K", [(64, 6), (32, 6), (128, 3)])
+@pytest.mark.parametrize("C,K", [(64, 6), (32, 6), (128, 3), (64, 8), (128, 7), (48, 5), (256, 12)])
 def test_head_ce_fwd_bwd(C, K):
     torch.manual_seed(2)
     N, H, W = 2, 24, 20
