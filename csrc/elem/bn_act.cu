@@ -105,6 +105,32 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Index math of the elementwise kernels.  A thread owns ONE 8-channel group for its whole life (the
+// launchers make the grid stride a multiple of the number of groups), so the group index and the
+// per-channel constants are computed once and a trip only advances the pixel.  Nothing in the loops
+// divides 64-bit numbers: that division is ~100 emulated instructions and made these kernels
+// issue-bound at 60 % of the HBM roofline.
+struct PixWalk {
+  int cv;                 // 8-channel group of this thread
+  long long pix, step;    // first pixel (or 2x2 window) and pixels per trip
+};
+__device__ __forceinline__ PixWalk pix_walk(int CV) {
+  const long long gs = (long long)gridDim.x * blockDim.x;      // multiple of CV (see grid_for_groups)
+  const long long idx0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  PixWalk w;
+  w.cv = (int)(idx0 % CV);
+  w.pix = idx0 / CV;
+  w.step = gs / CV;
+  return w;
+}
+// 2x2 window index -> top-left pixel of the window (32-bit arithmetic; the launchers check the range)
+__device__ __forceinline__ long long window_origin(long long win, int Wo, int Ho, int H, int W) {
+  const unsigned u = (unsigned)win;
+  const unsigned t = u / (unsigned)Wo, wo = u - t * (unsigned)Wo;
+  const unsigned n = t / (unsigned)Ho, ho = t - n * (unsigned)Ho;
+  return ((long long)n * H + 2 * ho) * W + 2 * wo;
+}
+
 template <bool POOL>
 __global__ void __launch_bounds__(kThreads)
 bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ y, long long ld_y,
@@ -112,49 +138,41 @@ bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ y, long long ld_y,
                         __nv_bfloat16* __restrict__ pool, long long ld_p, int N, int H, int W, int C) {
   const int CV = C >> 3;
   const long long P = (long long)N * H * W;
-  const long long items = (POOL ? P / 4 : P) * CV;
+  const long long items = POOL ? P / 4 : P;
   const int Wo = W >> 1, Ho = H >> 1;
-  int last_cv = -1;
+  const PixWalk wk = pix_walk(CV);
+  const int cv = wk.cv;
+  const long long ps = wk.step;
+  long long pix = wk.pix;
   float sc[8], sh[8];
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < items;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(idx % CV);
-    const long long pix = idx / CV;
-    if (cv != last_cv) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j); }
-      last_cv = cv;
-    }
-    if (!POOL) {
-      // when the grid stride is a multiple of CV the channel group is the same for the next trips:
-      // issue four loads before any math
-      const long long gs = (long long)gridDim.x * blockDim.x;
-      if (gs % CV == 0 && idx + 3 * gs < items) {
-        bf16x8 v[4];
+  for (int j = 0; j < 8; ++j) { sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j); }
+  if (!POOL) {
+    const __nv_bfloat16* yp = y + cv * 8;
+    __nv_bfloat16* op = out + cv * 8;
+    for (; pix + 3 * ps < items; pix += 4 * ps) {           // four loads in flight before any math
+      bf16x8 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = ld8(y + ((idx + u * gs) / CV) * ld_y + cv * 8);
+      for (int u = 0; u < 4; ++u) v[u] = ld8(yp + (pix + u * ps) * ld_y);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          float f[8];
-          unpack8(v[u], f);
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8(v[u], f);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
-          st8(out + ((idx + u * gs) / CV) * ld_o + cv * 8, pack8(f));
-        }
-        idx += 3 * gs;
-        continue;
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+        st8(op + (pix + u * ps) * ld_o, pack8(f));
       }
+    }
+    for (; pix < items; pix += ps) {
       float f[8];
-      unpack8(ld8(y + pix * ld_y + cv * 8), f);
+      unpack8(ld8(yp + pix * ld_y), f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
-      st8(out + pix * ld_o + cv * 8, pack8(f));
-    } else {
-      const int wo = (int)(pix % Wo);
-      const long long t = pix / Wo;
-      const int ho = (int)(t % Ho);
-      const long long n = t / Ho;
-      const long long p00 = (n * H + 2 * ho) * W + 2 * wo;
+      st8(op + pix * ld_o, pack8(f));
+    }
+  } else {
+    for (; pix < items; pix += ps) {
+      const long long p00 = window_origin(pix, Wo, Ho, H, W);
       bf16x8 in[4];
       in[0] = ld8(y + p00 * ld_y + cv * 8);
       in[1] = ld8(y + (p00 + 1) * ld_y + cv * 8);
@@ -276,13 +294,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
       }
     }
     for (; pix < items; pix += stride) {
-      long long p00 = 0;
-      if (POOL) {
-        const int wo = (int)(pix % Wo);
-        const long long t = pix / Wo;
-        const int ho = (int)(t % Ho);
-        p00 = ((t / Ho) * H + 2 * ho) * W + 2 * wo;
-      }
+      const long long p00 = POOL ? window_origin(pix, Wo, Ho, H, W) : 0;
       float yv[4][8], g[4][8];
       load_g<POOL>(d_out, ld_do, d_pool, ld_dp, y, ld_y, sc, sh, pix, p00, W, cv, yv, g);
 #pragma unroll
@@ -346,53 +358,44 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
                     __nv_bfloat16* __restrict__ dy, long long ld_dy) {
   const int CV = C >> 3;
   const long long P = (long long)N * H * W;
-  const long long items = (POOL ? P / 4 : P) * CV;
+  const long long items = POOL ? P / 4 : P;
   const int Wo = W >> 1, Ho = H >> 1;
-  int last_cv = -1;
+  const PixWalk wk = pix_walk(CV);
+  const int cv = wk.cv;
+  const long long ps = wk.step;
+  long long pix = wk.pix;
   float sc[8], sh[8], k1[8], e1[8], e0[8];
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < items;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(idx % CV);
-    const long long pix = idx / CV;
-    if (cv != last_cv) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j);
-        k1[j] = __ldg(coef + cv * 8 + j); e1[j] = __ldg(coef + C + cv * 8 + j);
-        e0[j] = __ldg(coef + 2 * C + cv * 8 + j);
-      }
-      last_cv = cv;
-    }
-    if (!POOL) {
-      const long long gs = (long long)gridDim.x * blockDim.x;
-      if (gs % CV == 0 && idx + gs < items) {              // two pixels per trip, loads first
-        const long long px1 = (idx + gs) / CV;
-        const bf16x8 y0 = ld8(y + pix * ld_y + cv * 8), y1 = ld8(y + px1 * ld_y + cv * 8);
-        bf16x8 d0 = y0, d1 = y1;
-        if (d_out != nullptr) { d0 = ld8(d_out + pix * ld_do + cv * 8); d1 = ld8(d_out + px1 * ld_do + cv * 8); }
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = __ldg(ss + cv * 8 + j); sh[j] = __ldg(ss + C + cv * 8 + j);
+    k1[j] = __ldg(coef + cv * 8 + j); e1[j] = __ldg(coef + C + cv * 8 + j);
+    e0[j] = __ldg(coef + 2 * C + cv * 8 + j);
+  }
+  if (!POOL) {
+    const __nv_bfloat16* yp = y + cv * 8;
+    const __nv_bfloat16* gp = d_out == nullptr ? nullptr : d_out + cv * 8;
+    __nv_bfloat16* op = dy + cv * 8;
+    for (; pix + ps < items; pix += 2 * ps) {              // two pixels per trip, loads first
+      const long long px1 = pix + ps;
+      const bf16x8 y0 = ld8(yp + pix * ld_y), y1 = ld8(yp + px1 * ld_y);
+      bf16x8 d0 = y0, d1 = y1;
+      if (gp != nullptr) { d0 = ld8(gp + pix * ld_do); d1 = ld8(gp + px1 * ld_do); }
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          float yf[8], gf[8], o[8];
-          unpack8(u ? y1 : y0, yf);
-          unpack8(u ? d1 : d0, gf);
+      for (int u = 0; u < 2; ++u) {
+        float yf[8], gf[8], o[8];
+        unpack8(u ? y1 : y0, yf);
+        unpack8(u ? d1 : d0, gf);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float gm = (d_out != nullptr && fmaf(yf[j], sc[j], sh[j]) > 0.f) ? gf[j] : 0.f;
-            o[j] = fmaf(k1[j], gm, fmaf(e1[j], yf[j], e0[j]));
-          }
-          st8(dy + (u ? px1 : pix) * ld_dy + cv * 8, pack8(o));
+        for (int j = 0; j < 8; ++j) {
+          const float gm = (gp != nullptr && fmaf(yf[j], sc[j], sh[j]) > 0.f) ? gf[j] : 0.f;
+          o[j] = fmaf(k1[j], gm, fmaf(e1[j], yf[j], e0[j]));
         }
-        idx += gs;
-        continue;
+        st8(op + (u ? px1 : pix) * ld_dy, pack8(o));
       }
     }
-    long long p00 = 0;
-    if (POOL) {
-      const int wo = (int)(pix % Wo);
-      const long long t = pix / Wo;
-      const int ho = (int)(t % Ho);
-      p00 = ((t / Ho) * H + 2 * ho) * W + 2 * wo;
-    }
+  }
+  for (; pix < items; pix += ps) {
+    const long long p00 = POOL ? window_origin(pix, Wo, Ho, H, W) : 0;
     float yv[4][8], g[4][8];
     load_g<POOL>(d_out, ld_do, d_pool, ld_dp, y, ld_y, sc, sh, pix, p00, W, cv, yv, g);
 #pragma unroll
@@ -409,6 +412,17 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
 }  // namespace b200
 
 using namespace b200;
+
+// Grid for the kernels that use pix_walk(): blocks * kThreads must be a multiple of the number of
+// 8-channel groups so that a thread keeps its group from trip to trip.
+static int grid_for_groups(long long pixels, int CV) {
+  int a = CV, b = kThreads;
+  while (b) { const int t = a % b; a = b; b = t; }          // a = gcd(CV, kThreads)
+  const int m = CV / a;
+  int g = grid_for(pixels * CV, kThreads);
+  g = (g / m) * m;
+  return g < m ? m : g;
+}
 
 extern "C" int b200seg_stats_rows() { return 4 * kNumSMs; }   // CTAs of the reduction kernels (4 per SM)
 
@@ -438,11 +452,12 @@ extern "C" int b200seg_bn_relu_pool_fwd(const void* y, long long ld_y, const flo
   const long long P = (long long)N * H * W;
   if (pool != nullptr) {
     if ((H | W) & 1) return (int)cudaErrorInvalidValue;
-    int grid = grid_for(P / 4 * (C / 8), kThreads);
+    if (P / 4 >= (1ll << 32)) return (int)cudaErrorInvalidValue;
+    int grid = grid_for_groups(P / 4, C / 8);
     bn_relu_pool_fwd_kernel<true><<<grid, kThreads, 0, st>>>(
         (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, (__nv_bfloat16*)pool, ld_p, N, H, W, C);
   } else {
-    int grid = grid_for(P * (C / 8), kThreads);
+    int grid = grid_for_groups(P, C / 8);
     bn_relu_pool_fwd_kernel<false><<<grid, kThreads, 0, st>>>(
         (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, nullptr, 0, N, H, W, C);
   }
@@ -460,6 +475,7 @@ extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, cons
   if (rows_pb < 1) return (int)cudaErrorInvalidValue;
   const int rows = b200seg_stats_rows();
   const long long P = (long long)N * H * W;
+  if (pooled && P / 4 >= (1ll << 32)) return (int)cudaErrorInvalidValue;
   float* partial = workspace;
   float* coef = workspace + (size_t)rows * 2 * C;
   size_t smem = (size_t)2 * rows_pb * C * sizeof(float);
@@ -472,11 +488,11 @@ extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, cons
   }
   bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
   if (pooled) {
-    int grid = grid_for(P / 4 * CV, kThreads);
+    int grid = grid_for_groups(P / 4, CV);
     bn_bwd_apply_kernel<true><<<grid, kThreads, 0, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, coef, N, H, W, C,
                                                          (__nv_bfloat16*)dy, ld_dy);
   } else {
-    int grid = grid_for(P * CV, kThreads);
+    int grid = grid_for_groups(P, CV);
     bn_bwd_apply_kernel<false><<<grid, kThreads, 0, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, coef, N, H, W, C,
                                                           (__nv_bfloat16*)dy, ld_dy);
   }

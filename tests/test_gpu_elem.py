@@ -17,10 +17,11 @@ def test_native_library_is_loaded():
     assert loader.library() is not None, loader.load_error()
 
 
-@pytest.mark.parametrize("C,pool", [(64, True), (32, False), (128, True), (16, False)])
+@pytest.mark.parametrize("C,pool", [(64, True), (32, False), (128, True), (16, False), (96, True), (192, False),
+                                    (64, False)])
 def test_bn_relu_pool_fwd_and_stats(C, pool):
     torch.manual_seed(0)
-    N, H, W = 3, 16, 24
+    N, H, W = (3, 16, 24) if C != 64 else (5, 96, 136)      # the large one runs several trips per thread
     y = _bf(torch.randn(N, H, W, C, device=DEV) * 2 + 0.5)
     part = torch.empty(torch.ops.b200seg.stats_rows(), 2, C, device=DEV)
     torch.ops.b200seg.channel_stats(y, part)
@@ -51,10 +52,11 @@ def test_bn_relu_pool_fwd_and_stats(C, pool):
         torch.testing.assert_close(pl.cpu().float(), p_ref.float(), rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("C,pool,with_dout", [(64, True, True), (32, False, True), (128, True, False)])
+@pytest.mark.parametrize("C,pool,with_dout", [(64, True, True), (32, False, True), (128, True, False),
+                                              (96, False, True), (192, True, True), (64, False, True)])
 def test_bn_relu_pool_bwd(C, pool, with_dout):
     torch.manual_seed(1)
-    N, H, W = 2, 16, 16
+    N, H, W = (2, 16, 16) if C != 64 else (5, 96, 136)
     y = _bf(torch.randn(N, H, W, C, device=DEV))
     gamma = torch.rand(C, device=DEV) + 0.5
     beta = torch.randn(C, device=DEV) * 0.3
