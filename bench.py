@@ -238,7 +238,7 @@ def run_own(args, dctx, torch):
         ms_e2e = timed(step_e2e, args.steps, dctx, torch)
         h2d, d2h = tr.loader.bytes_per_batch, 8
     extra = {"engine": "native", "conv": os.environ.get("B200SEG_CONV", "tcgen05"),
-             "comm": tr.sync.backend, "codec": args.codec, "cuda_graph": not args.no_graph,
+             "comm": ("fused" if tr.sync.fused else tr.sync.backend), "codec": args.codec, "cuda_graph": not args.no_graph,
              "allreduce": (tr.sync.native.algorithm if tr.sync.native is not None else None)}
     return _result(args, dctx, "own", ms, ms_e2e, clk, launches, h2d, d2h, extra)
 

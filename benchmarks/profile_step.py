@@ -24,7 +24,10 @@ def main():
     ap.add_argument("--tile", type=int, default=512)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--out", default="")
+    ap.add_argument("--comm", default="auto", help="under torchrun: native | fused | torch")
     a = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
     os.environ["B200SEG_CONV"] = a.conv
     from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
     tiles = synthetic_tiles(a.batch, a.tile, 6, 0)
@@ -32,8 +35,11 @@ def main():
         from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
         from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
         cfg = TrainConfig(base_channels=a.base_channels, tile=a.tile, batch_size=a.batch, sync_every=1, codec="fp32",
-                          world_size=1, train_tiles=a.batch, holdout_tiles=0, sample_images=0, cuda_graph=False,
+                          world_size=world, rank=rank, comm=a.comm, train_tiles=a.batch, holdout_tiles=0,
+                          sample_images=0, cuda_graph=False,
                           out_dir=os.path.join(ROOT, "gpurun_out", "prof_run"), device="cuda")
+        if world > 1:
+            cfg = cfg.apply_env()
         tr = Trainer(cfg, datasets=(tiles, None))
         img, lab = tiles.images.cuda(), tiles.labels.cuda()
 
@@ -74,9 +80,10 @@ def main():
     for ms, cnt, name in rows[:40]:
         lines.append(f"{ms:9.3f} ms {100 * ms / total:5.1f}%  x{cnt:6.1f}  {name[:110]}")
     text = "\n".join(lines)
-    print(text)
-    if a.out:
-        open(a.out, "w").write(text + "\n")
+    if rank == 0:
+        print(text)
+        if a.out:
+            open(a.out, "w").write(text + "\n")
 
 
 if __name__ == "__main__":

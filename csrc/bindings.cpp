@@ -256,6 +256,20 @@ void allreduce_nvls(at::IntArrayRef signal_ptrs, int64_t multicast_ptr, int64_t 
                             (float)post_scale, (unsigned int)epoch, (int)blocks, cur()), "allreduce_nvls");
 }
 
+void peer_barrier(at::IntArrayRef signal_ptrs, int64_t rank, int64_t epoch) {
+  const int world = (int)signal_ptrs.size();
+  TORCH_CHECK(world >= 2 && world <= 16, "peer_barrier: bad pointer list");
+  unsigned int* sp[16];
+  for (int r = 0; r < world; ++r) sp[r] = reinterpret_cast<unsigned int*>(signal_ptrs[r]);
+  ok(b200seg_barrier(sp, (int)rank, world, (unsigned int)epoch, cur()), "peer_barrier");
+}
+
+// multicast_ptr == 0 unregisters.  n_elems floats starting at buf are covered.
+void set_grad_multicast(const Tensor& buf, int64_t n_elems, int64_t multicast_ptr) {
+  ok(b200seg_set_grad_multicast(buf.data_ptr(), n_elems * 4, reinterpret_cast<const void*>(multicast_ptr)),
+     "set_grad_multicast");
+}
+
 void write_mult(const Tensor& scale, double levels, Tensor out) {
   c10::cuda::CUDAGuard g(out.device());
   ok(b200seg_write_mult(f32(scale), (float)levels, f32(out), cur()), "write_mult");
@@ -313,6 +327,8 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("write_mult(Tensor scale, float levels, Tensor(a!) out) -> ()", &write_mult);
   m.def("allreduce_nvls(int[] signal_ptrs, int multicast_ptr, int rank, int n_elems, float post_scale, int epoch, "
         "int blocks) -> ()", &allreduce_nvls);
+  m.def("peer_barrier(int[] signal_ptrs, int rank, int epoch) -> ()", &peer_barrier);
+  m.def("set_grad_multicast(Tensor buf, int n_elems, int multicast_ptr) -> ()", &set_grad_multicast);
   m.def("allreduce_signal_bytes() -> int", &allreduce_signal_bytes);
   m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);

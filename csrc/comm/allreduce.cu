@@ -205,6 +205,15 @@ allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, 
   cross_gpu_barrier(pp, rank, world, epoch + 1);
 }
 
+__global__ void barrier_kernel(PeerPtrs pp, int rank, int world, uint32_t epoch) {
+  cross_gpu_barrier(pp, rank, world, epoch);
+}
+
+// Registered multicast alias of the gradient buffer (fused wgrad -> all-reduce, see grad_red_add).
+static const char* g_mc_local = nullptr;
+static long long g_mc_bytes = 0;
+static long long g_mc_delta = 0;
+
 __global__ void write_mult_kernel(const float* scale, float levels, float* out) {
   *out = (levels > 0.f) ? __fdiv_rn(*scale, levels) : 1.f;
 }
@@ -216,6 +225,36 @@ using namespace b200;
 extern "C" int b200seg_write_mult(const float* scale, float levels, float* out, cudaStream_t st) {
   write_mult_kernel<<<1, 1, 0, st>>>(scale, levels, out);
   return (int)cudaGetLastError();
+}
+
+// One cross-GPU barrier on the signal pad (consumes ONE epoch of the same counter the all-reduces use).
+extern "C" int b200seg_barrier(unsigned int* const* signal_ptrs, int rank, int world, unsigned int epoch,
+                               cudaStream_t st) {
+  if (world < 2 || world > kMaxRanks) return (int)cudaErrorInvalidValue;
+  PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) pp.signal[r] = signal_ptrs[r];
+  barrier_kernel<<<1, 32, 0, st>>>(pp, rank, world, epoch);
+  return (int)cudaGetLastError();
+}
+
+// Fused weight-gradient + all-reduce: register [local_base, local_base + bytes) together with the
+// multicast address that aliases it on every rank.  From then on every weight-gradient launcher whose
+// destination lies inside the range adds through the multicast alias (one multimem.red per element,
+// fanned out by the NVSwitch into all replicas).  multicast_base == NULL unregisters.  Process-wide;
+// set it before capturing CUDA graphs (the alias is baked into the kernel arguments).
+extern "C" int b200seg_set_grad_multicast(const void* local_base, long long bytes, const void* multicast_base) {
+  if (multicast_base == nullptr || local_base == nullptr || bytes <= 0) {
+    g_mc_local = nullptr; g_mc_bytes = 0; g_mc_delta = 0;
+    return 0;
+  }
+  g_mc_local = static_cast<const char*>(local_base);
+  g_mc_bytes = bytes;
+  g_mc_delta = static_cast<const char*>(multicast_base) - static_cast<const char*>(local_base);
+  return 0;
+}
+extern "C" long long b200seg_grad_multicast_delta(const void* p) {
+  const char* c = static_cast<const char*>(p);
+  return (g_mc_local != nullptr && c >= g_mc_local && c < g_mc_local + g_mc_bytes) ? g_mc_delta : 0;
 }
 
 extern "C" int b200seg_allreduce_max_blocks() { return 256; }   // all co-resident: 4 x 512 threads per SM

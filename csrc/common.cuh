@@ -43,6 +43,51 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// Gradient accumulation that may be fused with the cross-GPU reduction: with mc_delta == 0 it is a
+// plain red.global.add into this GPU's gradient buffer; otherwise `p + mc_delta` is the NVSwitch
+// multicast alias of the same element and ONE multimem.red adds the value into every replica's buffer
+// (the switch fans the reduction out), so the weight-gradient GEMM epilogue IS the all-reduce.
+__device__ __forceinline__ void grad_red_add(float* p, float v, long long mc_delta) {
+  if (mc_delta == 0) {
+    atomicAdd(p, v);
+  } else {
+    asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(reinterpret_cast<char*>(p) + mc_delta),
+                 "f"(v)
+                 : "memory");
+  }
+}
+
+// Four consecutive floats through the multicast alias in one 16-byte multimem.red (4x fewer fabric
+// packets than the scalar form; the alias must be 16-byte aligned).
+__device__ __forceinline__ void grad_red_add4_mc(float* p, float a, float b, float c, float d, long long mc_delta) {
+  asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(
+                   reinterpret_cast<char*>(p) + mc_delta),
+               "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+// Register transpose inside lane quads.  In: lane holds row (lane), v[c] = column c.  Out: v[4g + i]
+// (i = 0..3) is the element of row (lane & ~3) + i, column 4g + (lane & 3) -- i.e. every lane ends up
+// with four CONSECUTIVE rows of one column, which is what a 16-byte vector reduction needs when rows
+// are the contiguous direction in memory.  4 shuffles per 4x4 block.
+__device__ __forceinline__ void quad_transpose32(uint32_t (&v)[32], int lane) {
+  const bool b0 = lane & 1, b1 = lane & 2;
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    uint32_t a0 = v[4 * g], a1 = v[4 * g + 1], a2 = v[4 * g + 2], a3 = v[4 * g + 3];
+    uint32_t t0 = b0 ? a0 : a1, t1 = b0 ? a2 : a3;
+    t0 = __shfl_xor_sync(0xffffffffu, t0, 1);
+    t1 = __shfl_xor_sync(0xffffffffu, t1, 1);
+    if (b0) { a0 = t0; a2 = t1; } else { a1 = t0; a3 = t1; }
+    t0 = b1 ? a0 : a2;
+    t1 = b1 ? a1 : a3;
+    t0 = __shfl_xor_sync(0xffffffffu, t0, 2);
+    t1 = __shfl_xor_sync(0xffffffffu, t1, 2);
+    if (b1) { a0 = t0; a1 = t1; } else { a2 = t0; a3 = t1; }
+    v[4 * g] = a0; v[4 * g + 1] = a1; v[4 * g + 2] = a2; v[4 * g + 3] = a3;
+  }
+}
+
 inline int grid_for(long long work_items, int threads, int max_blocks_per_sm = 8) {
   long long b = (work_items + threads - 1) / threads;
   long long cap = static_cast<long long>(kNumSMs) * max_blocks_per_sm;

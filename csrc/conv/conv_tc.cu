@@ -585,6 +585,7 @@ struct WgradParams {
   int H;                                    // convT: low-res height (Y = n*H + y)
   long long co_stride;                      // floats between consecutive output channels in dw
   int tap0;                                 // first filter tap handled (m_blocks counts taps from here)
+  long long mc_delta;                       // != 0: add through the multicast alias (fused all-reduce)
 };
 
 __global__ void __launch_bounds__(kConvThreads, 1)
@@ -704,7 +705,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
           }
           tmem_ld_wait();
-          if (row_ok) {
+          if (p.mc_delta != 0) {                              // fused all-reduce: 16-byte multicast reductions
+            quad_transpose32(r, lane);
+            float* qbase = base - (lane & 3);
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const int cj = c0 + 4 * g + (lane & 3);
+              const int co = co_base + cj;
+              if (row_ok && cj < p.block_n && co < co_lim)
+                grad_red_add4_mc(qbase + (size_t)co * co_stride, __uint_as_float(r[4 * g]),
+                                 __uint_as_float(r[4 * g + 1]), __uint_as_float(r[4 * g + 2]),
+                                 __uint_as_float(r[4 * g + 3]), p.mc_delta);
+            }
+          } else if (row_ok) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const int co = co_base + c0 + j;
@@ -1029,6 +1042,7 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   if (ks > p.p_tiles) ks = p.p_tiles;
   p.k_slices = ks;
   p.dw = dw;
+  p.mc_delta = b200seg_grad_multicast_delta(dw);
   CUtensorMap mx, mdy;
   const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
   {

@@ -53,6 +53,7 @@ struct WgradStripParams {
   int ctas_per_group;
   int wsegs, rows_per_piece, pieces_per_col, pieces;   // pieces per group
   float* dw;
+  long long mc_delta;                  // != 0: add through the multicast alias (fused all-reduce)
 };
 
 template <int BN>
@@ -184,6 +185,18 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         uint32_t v[32];
         tmem_ld_32x32b_x32(t_addr + c0, v);
         tmem_ld_wait();
+        if (p.mc_delta != 0) {                                // fused all-reduce: 16-byte multicast reductions
+          quad_transpose32(v, lane);
+          float* qbase = base - (lane & 3);                   // first of the quad's four channels
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int co = n_tile * BN + c0 + 4 * g + (lane & 3);
+            if (row_ok && co < p.Cout)
+              grad_red_add4_mc(qbase + (size_t)co * co_stride, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+                               __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]), p.mc_delta);
+          }
+          continue;
+        }
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int co = n_tile * BN + c0 + j;
@@ -253,6 +266,7 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
   if (cpg > p.pieces) cpg = p.pieces;
   p.ctas_per_group = cpg;
   p.dw = dw;
+  p.mc_delta = b200seg_grad_multicast_delta(dw);
   CUtensorMap mx, mdy;
   {
     long long dims[4] = {Cin, W, H, N}, str[4] = {1, ld_x, ld_x * W, ld_x * W * H};

@@ -56,7 +56,7 @@ class TrainConfig:
     compress_level: int = 1          # mgzip compresslevel (R:51)
     compress_threads: int = 12       # mgzip thread count (R:43)
     compress_block: int = 1_000_000  # mgzip blocksize (R:51)
-    comm: str = "auto"               # auto | native | torch | star
+    comm: str = "auto"               # auto | native | fused | torch | star
     bucket_mb: float = 25.0
     # ---- runtime ---------------------------------------------------------------------------
     device: str = "auto"             # auto | cuda | cpu

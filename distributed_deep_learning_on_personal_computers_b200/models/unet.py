@@ -164,17 +164,35 @@ class UNet(nn.Module):
     def flatten_parameters(self, device=None) -> Dict[str, torch.Tensor]:
         """Move every parameter into one flat fp32 buffer (+ a zeroed flat ``.grad`` buffer).
 
-        Order = ``parameters()`` order = the reference's gradient wire order (R:453).  Returns
-        ``{"param", "grad", "offsets"}``; ``offsets[name] = (start, numel)`` in elements.
+        Layout: first the *bulk* tensors — the 3x3 / transposed-conv weights whose gradients the
+        tensor-core wgrad kernels write (everything but the 3-channel stem and the 1x1 head) — in
+        ``parameters()`` order (the reference's wire order, R:453), then all the small tensors (BN
+        affine, biases, stem, head).  The split lets the fused exchange treat the two regions
+        differently (``parallel/allreduce.py``).  Returns ``{"param", "grad", "offsets", "bulk_elems"}``;
+        ``offsets[name] = (start, numel)`` in elements.  Nothing depends on the order: every consumer
+        goes through ``offsets`` and checkpoints are by name.
         """
         params = list(self.named_parameters())
         device = device or params[0][1].device
         convT = {n for n, m in self.named_modules() if isinstance(m, nn.ConvTranspose2d)}
+
+        def is_bulk(name, p):
+            if p.dim() != 4 or p.shape[-1] * p.shape[-2] == 1:
+                return False
+            cin = p.shape[0] if name.rsplit(".", 1)[0] in convT else p.shape[1]
+            return cin % 8 == 0
+
         offsets: "OrderedDict[str, Tuple[int, int]]" = OrderedDict()
         total = 0
-        for name, p in params:
-            offsets[name] = (total, p.numel())
-            total += (p.numel() + FLAT_ALIGN - 1) // FLAT_ALIGN * FLAT_ALIGN
+        bulk_elems = 0
+        for want_bulk in (True, False):
+            for name, p in params:
+                if is_bulk(name, p) != want_bulk:
+                    continue
+                offsets[name] = (total, p.numel())
+                total += (p.numel() + FLAT_ALIGN - 1) // FLAT_ALIGN * FLAT_ALIGN
+            if want_bulk:
+                bulk_elems = total
         flat_p = torch.zeros(total, dtype=torch.float32, device=device)
         flat_g = torch.zeros(total, dtype=torch.float32, device=device)
         with torch.no_grad():
@@ -187,7 +205,7 @@ class UNet(nn.Module):
                 p.grad = self._internal_view(flat_g, off, p, is_t)
         for _, buf in self.named_buffers():
             buf.data = buf.data.to(device)
-        self._flat = {"param": flat_p, "grad": flat_g, "offsets": offsets}
+        self._flat = {"param": flat_p, "grad": flat_g, "offsets": offsets, "bulk_elems": bulk_elems}
         return self._flat
 
     @property

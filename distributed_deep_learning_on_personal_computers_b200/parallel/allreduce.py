@@ -41,7 +41,8 @@ from .dist import DistContext
 class GradientSynchronizer:
     def __init__(self, flat_grad: torch.Tensor, ctx: DistContext, codec: str = "fp32",
                  reduce: str = "mean", accumulate: str = "mean", backend: str = "auto",
-                 requantize_output: bool = False, star=None, bucket_mb: float = 25.0):
+                 requantize_output: bool = False, star=None, bucket_mb: float = 25.0,
+                 fused_bulk_elems: int = 0):
         self.flat = flat_grad
         self.ctx = ctx
         self.codec: Codec = get_codec(codec)
@@ -55,11 +56,19 @@ class GradientSynchronizer:
             if star is None and flat_grad.is_cuda and ctx.world_size > 1:
                 from . import symm
                 backend = "native" if symm.available(ctx) else "torch"
+        # "fused": native transport with the bulk of the buffer reduced inside the wgrad kernels
+        # (multimem.red through the NVSwitch multicast alias); falls back to "native" on one rank.
+        self.fused = backend == "fused" and ctx.world_size > 1
+        if backend == "fused":
+            backend = "native"
+            if ctx.world_size > 1 and self.codec.name != "fp32":
+                raise ValueError("comm=fused reduces in fp32 inside the wgrad kernels; use codec fp32")
         self.backend = backend
         self.native = None
         if backend == "native" and ctx.world_size > 1:
             from . import symm
-            self.native = symm.SymmetricAllReduce(flat_grad, ctx, self.codec)
+            self.native = symm.SymmetricAllReduce(flat_grad, ctx, self.codec,
+                                                  fused_bulk_elems=fused_bulk_elems if self.fused else 0)
             self.flat = self.native.buffer          # gradients now live in symmetric memory
         self.timings: Dict[str, float] = {}
         self.bytes_on_wire = 0
@@ -88,6 +97,11 @@ class GradientSynchronizer:
             self._roundtrip_local()
         self.timings["sync_s"] = time.perf_counter() - t0
         return self._post_scale(k_accum)
+
+    def after_step(self) -> None:
+        """Call once the optimizer has consumed (and zeroed) the gradient buffer."""
+        if self.fused and self.native is not None:
+            self.native.barrier()
 
     # -- torch.distributed -------------------------------------------------------------------
     def _roundtrip_local(self) -> None:

@@ -47,7 +47,7 @@ def available(ctx: DistContext) -> bool:
 
 class SymmetricAllReduce:
     def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None,
-                 algorithm: str = "auto"):
+                 algorithm: str = "auto", fused_bulk_elems: int = 0):
         import torch.distributed._symmetric_memory as symm_mem
         from ..ops import loader
         if loader.library() is None:
@@ -83,7 +83,7 @@ class SymmetricAllReduce:
         self.sig_ptrs = [int(p) for p in self.h_sig.buffer_ptrs]
         self.wire_ptrs = [int(p) for p in self.h_wire.buffer_ptrs] if self.h_wire else self.grad_ptrs
         self.mult_ptrs = [p + self.mult_off for p in self.sig_ptrs] if codec.needs_scale else []
-        self.calls = 0
+        self.epoch = 1                                           # next free barrier epoch
         per_rank_vecs = self.n // 4 // max(ctx.world_size, 1)
         self.blocks = int(min(ops.allreduce_max_blocks(), max(8, per_rank_vecs // 1024)))
         # algorithm: "twoshot" (peer loads/stores), "nvls" (in-switch multimem reduction, fp32 wire),
@@ -105,6 +105,20 @@ class SymmetricAllReduce:
         self.oneshot_out: Optional[torch.Tensor] = None
         if self.n * 4 <= ONESHOT_MAX_BYTES and self.algorithm != "nvls" or self.algorithm == "oneshot":
             self.oneshot_out = torch.empty(self.n, dtype=torch.float32, device=dev)
+        # Fused mode: the first `fused_bulk_elems` floats (the conv / convT weight gradients) are reduced
+        # by the wgrad kernels themselves -- their epilogues add through the multicast alias, i.e. into
+        # every replica at once (csrc/common.cuh grad_red_add).  Only the small tail goes through an
+        # all-reduce kernel, whose entry barrier is also what orders those remote adds before the
+        # optimizer reads the buffer.
+        self.fused_bulk = 0
+        if fused_bulk_elems:
+            if not (self.multicast_ptr and codec.name == "fp32"):
+                raise RuntimeError("fused wgrad+all-reduce needs NVSwitch multicast and the fp32 codec")
+            if fused_bulk_elems % 64 or fused_bulk_elems > n:
+                raise ValueError("fused_bulk_elems must be a multiple of 64 within the buffer")
+            self.fused_bulk = int(fused_bulk_elems)
+            ops.set_grad_multicast(self.buffer_full, self.fused_bulk, self.multicast_ptr)
+            self.tail_n = self.n - self.fused_bulk
         torch.cuda.synchronize(dev)
         dist.barrier(device_ids=[dev.index])
 
@@ -129,8 +143,19 @@ class SymmetricAllReduce:
                 levels = c.levels if c.levels is not None else 448.0
                 ops.write_mult(scale, float(levels), self.mult_slot)
                 Fn._tick()
-        epoch = 2 * self.calls + 1
-        self.calls += 1
+        epoch = self.epoch
+        self.epoch += 2
+        if self.fused_bulk:
+            if self.tail_n:
+                off = self.fused_bulk * 4
+                ops.allreduce_nvls(self.sig_ptrs, self.multicast_ptr + off, self.ctx.rank, self.tail_n,
+                                   float(post_scale), epoch, 8)
+            else:
+                ops.peer_barrier(self.sig_ptrs, self.ctx.rank, epoch)
+            Fn._tick()
+            if post_scale != 1.0:
+                self.buffer_full[:self.fused_bulk].mul_(post_scale)
+            return self.buffer
         if self.algorithm == "nvls":
             ops.allreduce_nvls(self.sig_ptrs, self.multicast_ptr, self.ctx.rank, self.n, float(post_scale), epoch,
                                self.blocks)
@@ -142,3 +167,18 @@ class SymmetricAllReduce:
         if self.oneshot_out is not None:
             self.buffer_full.copy_(self.oneshot_out)
         return self.buffer
+
+    @torch.no_grad()
+    def barrier(self) -> None:
+        """Cross-GPU barrier on the launching stream (one epoch).  Fused mode calls it after the
+        optimizer step: no rank may start adding into a peer's gradient buffer before that peer has
+        consumed and zeroed it."""
+        from ..ops import functional as Fn
+        torch.ops.b200seg.peer_barrier(self.sig_ptrs, self.ctx.rank, self.epoch)
+        self.epoch += 1
+        Fn._tick()
+
+    def close(self) -> None:
+        if self.fused_bulk:
+            torch.ops.b200seg.set_grad_multicast(self.buffer_full, 0, 0)
+            self.fused_bulk = 0

@@ -59,11 +59,15 @@ class Trainer:
         self.sync = GradientSynchronizer(
             self.model.flat["grad"], self.ctx, codec=cfg.codec, reduce=cfg.reduce,
             accumulate=cfg.accumulate, backend=("auto" if comm == "auto" else comm),
-            requantize_output=cfg.requantize_output, star=self.star, bucket_mb=cfg.bucket_mb)
+            requantize_output=cfg.requantize_output, star=self.star, bucket_mb=cfg.bucket_mb,
+            fused_bulk_elems=self.model.flat.get("bulk_elems", 0))
         if self.sync.flat is not self.model.flat["grad"]:
             self._rebind_grad(self.sync.flat)
 
         self.engine_kind = cfg.engine if cfg.engine != "auto" else "native"
+        if self.sync.fused and (self.engine_kind != "native" or os.environ.get("B200SEG_CONV", "") == "cudnn"):
+            raise ValueError("comm=fused needs the native engine with the tcgen05 wgrad kernels "
+                             "(they are what performs the reduction)")
         self.engine: Optional[NativeEngine] = None
         self._engine_shape = None
         self.optimizer = build_optimizer(self.model, cfg)
@@ -178,6 +182,7 @@ class Trainer:
             self.optimizer.step(grad_scale=scale, zero_grad=True)
             if self.engine is not None and self.optimizer.p_lowp is None:
                 self.engine.refresh_lowp()
+            self.sync.after_step()
         self.pending = 0
 
     # -- epochs --------------------------------------------------------------------------------------
@@ -304,6 +309,8 @@ class Trainer:
     def close(self) -> None:
         if self.star is not None:
             self.star.close()
+        if getattr(self.sync, "native", None) is not None:
+            self.sync.native.close()
         self.ctx.shutdown()
 
 

@@ -123,6 +123,15 @@ int b200conv_convT_dgrad(const void* d_up, long long ld_g, const void* w, void* 
 int b200conv_convT_wgrad(const void* x, long long ld_x, const void* d_up, long long ld_g, float* dw, int N,
                          int h, int w_, int Cin, int Cout, cudaStream_t st);
 
+/* One cross-GPU barrier over the all-reduce signal pads (one epoch of the shared counter). */
+int b200seg_barrier(unsigned int* const* signal_ptrs, int rank, int world, unsigned int epoch, cudaStream_t st);
+/* Fused weight-gradient + all-reduce (no counterpart in the reference: its exchange is a separate TCP
+ * round, R:255-556).  Registers the multicast alias of the gradient buffer; weight-gradient launchers
+ * whose destination lies inside [local_base, local_base + bytes) then add with multimem.red through
+ * the alias, i.e. into every replica at once.  multicast_base == NULL unregisters. */
+int b200seg_set_grad_multicast(const void* local_base, long long bytes, const void* multicast_base);
+long long b200seg_grad_multicast_delta(const void* p);
+
 #ifdef __cplusplus
 }
 #endif

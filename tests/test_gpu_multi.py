@@ -129,3 +129,84 @@ def test_two_rank_training_replicas_identical(comm, tmp_path):
     assert b0 == b1 == comm
     assert d0 == d1                                  # bit-identical replicas
     assert l0[-1] < l0[0]
+
+
+def _fused_worker(rank, world, port, q, out_dir):
+    """Gradients reduced inside the wgrad epilogues (multimem.red through the multicast alias) against
+    the same micro-batch accumulated locally and summed by NCCL."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
+    from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
+    cfg = TrainConfig(base_channels=32, tile=128, train_tiles=8, holdout_tiles=0, batch_size=2, sync_every=1,
+                      epochs=1, codec="fp32", comm="fused", device="cuda", out_dir=out_dir, sample_images=0,
+                      cuda_graph=False, timeout_s=120).apply_env()
+    tr = Trainer(cfg)
+    res = {"fused": tr.sync.fused, "bulk": tr.sync.native.fused_bulk if tr.sync.native else 0,
+           "n": tr.sync.flat.numel()}
+    tiles = synthetic_tiles(2, 128, 6, 10 + rank)
+    img, lab = tiles.images.cuda(), tiles.labels.cuda()
+    errs = []
+    for rep in range(3):
+        tr.sync.flat.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        tr.micro_step(img, lab)
+        tr.sync.sync(1)
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        g_fused = tr.sync.flat.clone()
+        # the same micro-batch, accumulated locally and summed by NCCL
+        nat = tr.sync.native
+        torch.ops.b200seg.set_grad_multicast(nat.buffer_full, 0, 0)
+        tr.sync.flat.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        tr.micro_step(img, lab)
+        g_ref = tr.sync.flat.clone()
+        dist.all_reduce(g_ref)
+        torch.ops.b200seg.set_grad_multicast(nat.buffer_full, nat.fused_bulk, nat.multicast_ptr)
+        scale = g_ref.abs().max().item()
+        errs.append(((g_fused - g_ref).abs().max().item(), scale,
+                     (g_fused[:nat.fused_bulk] - g_ref[:nat.fused_bulk]).abs().max().item()))
+    res["errs"] = errs
+    # a few real steps: loss goes down, replicas stay together
+    tr.sync.flat.zero_()
+    torch.cuda.synchronize()
+    dist.barrier(device_ids=[rank])
+    losses = []
+    for _ in range(3):
+        losses.append(tr.train_epoch()["mean_loss"])
+        tr.epoch += 1
+    chk = tr.model.flat["param"].double().sum().reshape(1)
+    lst = [torch.zeros_like(chk) for _ in range(world)]
+    dist.all_gather(lst, chk)
+    res["losses"] = losses
+    res["param_sums"] = [t.item() for t in lst]
+    if rank == 0:
+        q.put(res)
+    tr.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_fused_wgrad_allreduce_matches_local_plus_nccl(tmp_path):
+    world = min(torch.cuda.device_count(), 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fused_worker, args=(r, world, port, q, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    print(res)
+    assert res["fused"] and 0 < res["bulk"] < res["n"]
+    for err, scale, err_bulk in res["errs"]:
+        assert err <= 2e-4 * scale + 1e-6, res["errs"]
+    assert res["losses"][-1] < res["losses"][0]
+    s = res["param_sums"]
+    assert max(s) - min(s) <= 1e-6 * max(abs(s[0]), 1.0), s        # replicas agree to rounding
