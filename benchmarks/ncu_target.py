@@ -27,9 +27,16 @@ cfg = TrainConfig(base_channels=a.base_channels, tile=a.tile, batch_size=a.batch
                   out_dir=os.path.join(ROOT, "gpurun_out", "ncu_run"), device="cuda")
 tr = Trainer(cfg, datasets=(tiles, None))
 img, lab = tiles.images.cuda(), tiles.labels.cuda()
-for _ in range(a.steps):
+for i in range(a.steps):
+    last = i == a.steps - 1
+    if last:                                   # ncu --profile-from-start off captures exactly this step
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     tr.micro_step(img, lab)
     tr.pending = 1
     tr.sync_and_step()
+    if last:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
 torch.cuda.synchronize()
 print("ok")

@@ -1,5 +1,6 @@
 // Small device helpers shared by the memory-bound kernels.
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -86,6 +87,35 @@ __device__ __forceinline__ void quad_transpose32(uint32_t (&v)[32], int lane) {
     if (b1) { a0 = t0; a1 = t1; } else { a2 = t0; a3 = t1; }
     v[4 * g] = a0; v[4 * g + 1] = a1; v[4 * g + 2] = a2; v[4 * g + 3] = a3;
   }
+}
+
+// Programmatic dependent launch (B200SEG_PDL=1): a kernel may be scheduled while its predecessor in the
+// stream drains; pdl_wait() blocks until the predecessor has completed and its writes are visible, so
+// everything before it (barrier init, TMEM allocation, descriptor prefetch, CTA ramp-up) overlaps the
+// predecessor's tail.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_PDL"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 inline int grid_for(long long work_items, int threads, int max_blocks_per_sm = 8) {

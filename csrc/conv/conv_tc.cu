@@ -131,6 +131,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
+  pdl_wait();                 // everything above overlapped the previous kernel's tail (see common.cuh)
+  pdl_trigger();
   if (p.bias != nullptr) {
     for (int c = threadIdx.x; c < p.block_n; c += kTapThreads) {
       const int col = (blockIdx.x % p.n_tiles) * p.block_n + c;
@@ -618,6 +620,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                 // everything above overlapped the previous kernel's tail (see common.cuh)
+  pdl_trigger();
   const uint32_t tmem_base = tmem_base_s;
   const int nblocks = (p.block_n + 63) >> 6;
 
@@ -776,8 +780,7 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
     attr_done = true;
   }
   if (p.cluster == 1) {
-    tap_gemm_kernel<BK, BMN, STRIP><<<grid, kTapThreads, smem, st>>>(ma, mb, mo, p);
-    return (int)cudaGetLastError();
+    return (int)launch_k(tap_gemm_kernel<BK, BMN, STRIP>, grid, kTapThreads, smem, st, ma, mb, mo, p);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
@@ -1068,8 +1071,7 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
     attr_done = true;
   }
   const size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
-  wgrad_kernel<<<base_items * ks, kConvThreads, smem, st>>>(mx, mdy, p);
-  return (int)cudaGetLastError();
+  return (int)launch_k(wgrad_kernel, base_items * ks, kConvThreads, smem, st, mx, mdy, p);
 }
 
 extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout);

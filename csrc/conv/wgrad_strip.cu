@@ -85,6 +85,8 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();
+  pdl_trigger();
   const uint32_t tmem_base = tmem_base_s;
   const bool has_work = member < p.pieces;
 
@@ -244,8 +246,7 @@ static int launch_strip(const CUtensorMap& mx, const CUtensorMap& mdy, const Wgr
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
-  wgrad_strip_kernel<BN><<<grid, kWsThreads, smem, st>>>(mx, mdy, p);
-  return (int)cudaGetLastError();
+  return (int)launch_k(wgrad_strip_kernel<BN>, grid, kWsThreads, smem, st, mx, mdy, p);
 }
 
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,

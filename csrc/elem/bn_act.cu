@@ -21,6 +21,8 @@ constexpr int kThreads = 256;
 __global__ void __launch_bounds__(kThreads)
 channel_stats_kernel(const __nv_bfloat16* __restrict__ y, long long P, int C, long long ld,
                      float* __restrict__ partial) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float sm[];
   const int CV = C >> 3;
   const int rows_pb = kThreads / CV;
@@ -69,6 +71,8 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int rows, 
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    long long* __restrict__ nbt, float* __restrict__ ss, int C,
                                    float momentum, float eps, int training) {
+  pdl_wait();
+  pdl_trigger();
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= C) return;
@@ -136,6 +140,8 @@ __global__ void __launch_bounds__(kThreads)
 bn_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ y, long long ld_y,
                         const float* __restrict__ ss, __nv_bfloat16* __restrict__ out, long long ld_o,
                         __nv_bfloat16* __restrict__ pool, long long ld_p, int N, int H, int W, int C) {
+  pdl_wait();
+  pdl_trigger();
   const int CV = C >> 3;
   const long long P = (long long)N * H * W;
   const long long items = POOL ? P / 4 : P;
@@ -253,6 +259,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
                      const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
                      const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
                      int N, int H, int W, int C, float* __restrict__ partial) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float sm[];
   const int CV = C >> 3;
   const int rows_pb = kThreads / CV;
@@ -327,6 +335,8 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
                                        const float* __restrict__ gamma, const float* __restrict__ ss,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ coef, int C) {
+  pdl_wait();
+  pdl_trigger();
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= C) return;
@@ -356,6 +366,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
                     const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
                     const float* __restrict__ coef, int N, int H, int W, int C,
                     __nv_bfloat16* __restrict__ dy, long long ld_dy) {
+  pdl_wait();
+  pdl_trigger();
   const int CV = C >> 3;
   const long long P = (long long)N * H * W;
   const long long items = POOL ? P / 4 : P;
@@ -432,7 +444,7 @@ extern "C" int b200seg_channel_stats(const void* y, long long P, int C, long lon
   const int CV = C / 8, rows_pb = kThreads / CV;
   if (rows_pb < 1) return (int)cudaErrorInvalidValue;
   size_t smem = (size_t)2 * rows_pb * C * sizeof(float);
-  channel_stats_kernel<<<rows, kThreads, smem, st>>>((const __nv_bfloat16*)y, P, C, ld, partial);
+  launch_k(channel_stats_kernel, rows, kThreads, smem, st, (const __nv_bfloat16*)y, P, C, ld, partial);
   return (int)cudaGetLastError();
 }
 
@@ -440,8 +452,8 @@ extern "C" int b200seg_bn_finalize(const float* partial, int rows, long long cou
                                    const float* beta, const float* conv_bias, float* running_mean,
                                    float* running_var, long long* nbt, float* ss, int C, float momentum,
                                    float eps, int training, cudaStream_t st) {
-  bn_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, count, gamma, beta, conv_bias, running_mean,
-                                                  running_var, nbt, ss, C, momentum, eps, training);
+  launch_k(bn_finalize_kernel, (C + 3) / 4, 128, 0, st, partial, rows, count, gamma, beta, conv_bias, running_mean,
+           running_var, nbt, ss, C, momentum, eps, training);
   return (int)cudaGetLastError();
 }
 
@@ -454,12 +466,12 @@ extern "C" int b200seg_bn_relu_pool_fwd(const void* y, long long ld_y, const flo
     if ((H | W) & 1) return (int)cudaErrorInvalidValue;
     if (P / 4 >= (1ll << 32)) return (int)cudaErrorInvalidValue;
     int grid = grid_for_groups(P / 4, C / 8);
-    bn_relu_pool_fwd_kernel<true><<<grid, kThreads, 0, st>>>(
-        (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, (__nv_bfloat16*)pool, ld_p, N, H, W, C);
+    launch_k(bn_relu_pool_fwd_kernel<true>, grid, kThreads, 0, st,
+             (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, (__nv_bfloat16*)pool, ld_p, N, H, W, C);
   } else {
     int grid = grid_for_groups(P, C / 8);
-    bn_relu_pool_fwd_kernel<false><<<grid, kThreads, 0, st>>>(
-        (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, nullptr, 0, N, H, W, C);
+    launch_k(bn_relu_pool_fwd_kernel<false>, grid, kThreads, 0, st,
+             (const __nv_bfloat16*)y, ld_y, ss, (__nv_bfloat16*)out, ld_o, nullptr, 0, N, H, W, C);
   }
   return (int)cudaGetLastError();
 }
@@ -482,19 +494,20 @@ extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, cons
   const __nv_bfloat16 *a = (const __nv_bfloat16*)d_out, *b = (const __nv_bfloat16*)d_pool,
                       *yy = (const __nv_bfloat16*)y;
   if (pooled) {
-    bn_bwd_reduce_kernel<true><<<rows, kThreads, smem, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, N, H, W, C, partial);
+    launch_k(bn_bwd_reduce_kernel<true>, rows, kThreads, smem, st, a, ld_do, b, ld_dp, yy, ld_y, ss, N, H, W, C, partial);
   } else {
-    bn_bwd_reduce_kernel<false><<<rows, kThreads, smem, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, N, H, W, C, partial);
+    launch_k(bn_bwd_reduce_kernel<false>, rows, kThreads, smem, st, a, ld_do, nullptr, 0, yy, ld_y, ss, N, H, W, C,
+             partial);
   }
-  bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, st>>>(partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
+  launch_k(bn_bwd_finalize_kernel, (C + 3) / 4, 128, 0, st, partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
   if (pooled) {
     int grid = grid_for_groups(P / 4, CV);
-    bn_bwd_apply_kernel<true><<<grid, kThreads, 0, st>>>(a, ld_do, b, ld_dp, yy, ld_y, ss, coef, N, H, W, C,
-                                                         (__nv_bfloat16*)dy, ld_dy);
+    launch_k(bn_bwd_apply_kernel<true>, grid, kThreads, 0, st, a, ld_do, b, ld_dp, yy, ld_y, ss, coef, N, H, W, C,
+             (__nv_bfloat16*)dy, ld_dy);
   } else {
     int grid = grid_for_groups(P, CV);
-    bn_bwd_apply_kernel<false><<<grid, kThreads, 0, st>>>(a, ld_do, nullptr, 0, yy, ld_y, ss, coef, N, H, W, C,
-                                                          (__nv_bfloat16*)dy, ld_dy);
+    launch_k(bn_bwd_apply_kernel<false>, grid, kThreads, 0, st, a, ld_do, nullptr, 0, yy, ld_y, ss, coef, N, H, W, C,
+             (__nv_bfloat16*)dy, ld_dy);
   }
   return (int)cudaGetLastError();
 }

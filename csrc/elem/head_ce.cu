@@ -239,6 +239,8 @@ head_ce_fast_kernel(const __nv_bfloat16* __restrict__ a, long long ld_a, const f
                     float* __restrict__ db, uint8_t* __restrict__ pred, float* __restrict__ loss_acc,
                     float* __restrict__ workspace, unsigned int* __restrict__ counter) {
   extern __shared__ __align__(16) uint8_t smraw[];
+  pdl_wait();
+  pdl_trigger();
   constexpr int kHfPix = HfCfg<CT>::kPix, kHfTile = HfCfg<CT>::kTile;
   constexpr int pitch = CT + 8;                               // bf16 elements per tile row
   constexpr int CV = CT / 8;                                  // 16-byte pieces per pixel
@@ -475,10 +477,9 @@ static int launch_head_fast(const void* a, long long ld_a, const float* w, const
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
-  head_ce_fast_kernel<KT, CT><<<grid, kHfWarps * 32, smem, st>>>(
-      (const __nv_bfloat16*)a, ld_a, w, bias, labels, P, K, grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred,
-      loss_acc, ws, counter);
-  return (int)cudaGetLastError();
+  return (int)launch_k(head_ce_fast_kernel<KT, CT>, grid, kHfWarps * 32, smem, st, (const __nv_bfloat16*)a, ld_a, w,
+                       bias, (const uint8_t*)labels, P, K, grad_scale, (__nv_bfloat16*)da, ld_da, dw, db,
+                       (uint8_t*)pred, loss_acc, ws, counter);
 }
 
 static int head_fast_env() {           // B200SEG_HEAD_FAST=0 keeps the generic kernel (A/B runs)
