@@ -588,6 +588,7 @@ struct WgradParams {
   long long co_stride;                      // floats between consecutive output channels in dw
   int tap0;                                 // first filter tap handled (m_blocks counts taps from here)
   long long mc_delta;                       // != 0: add through the multicast alias (fused all-reduce)
+  int quads;                                // convT: output quadrants per CTA (4 = all share one x tile), else 1
 };
 
 __global__ void __launch_bounds__(kConvThreads, 1)
@@ -650,10 +651,13 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             for (int nb = 0; nb < nblocks; ++nb)
               tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
           } else {
-            const int q = n_tile / p.nt_per_q, nt = n_tile % p.nt_per_q;
-            for (int nb = 0; nb < nblocks; ++nb)
-              tma_load_5d(sb + nb * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0, q >> 1,
-                          n0 * p.H + h0);
+            for (int qi = 0; qi < p.quads; ++qi) {
+              const int q = p.quads == 4 ? qi : n_tile / p.nt_per_q;
+              const int nt = p.quads == 4 ? n_tile : n_tile % p.nt_per_q;
+              for (int nb = 0; nb < nblocks; ++nb)
+                tma_load_5d(sb + (qi * nblocks + nb) * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64,
+                            q & 1, w0, q >> 1, n0 * p.H + h0);
+            }
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -668,12 +672,23 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
           const uint64_t db0 = make_smem_desc(sa + p.a_bytes, 8192, 1024, LAYOUT_SW128);
-          for (int t = 0; t < p.mt; ++t) {                  // the M tiles of this CTA share the dy tile
-            const uint64_t da0 = make_smem_desc(sa + t * 16384, 8192, 1024, LAYOUT_SW128);
+          if (p.quads == 4) {                               // convT: the four quadrants share the x tile
+            const uint64_t da0 = make_smem_desc(sa, 8192, 1024, LAYOUT_SW128);
+            for (int qi = 0; qi < 4; ++qi) {
+              const uint64_t dbq = db0 + ((qi * nblocks * 8192) >> 4);
 #pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4)
-              umma_bf16(tmem_base + t * 256, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
-                        (it | k4) != 0 ? 1u : 0u);
+              for (int k4 = 0; k4 < 4; ++k4)
+                umma_bf16(tmem_base + qi * 128, da0 + ((k4 * 2048) >> 4), dbq + ((k4 * 2048) >> 4), idesc,
+                          (it | k4) != 0 ? 1u : 0u);
+            }
+          } else {
+            for (int t = 0; t < p.mt; ++t) {                // the M tiles of this CTA share the dy tile
+              const uint64_t da0 = make_smem_desc(sa + t * 16384, 8192, 1024, LAYOUT_SW128);
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                umma_bf16(tmem_base + t * 256, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
+                          (it | k4) != 0 ? 1u : 0u);
+            }
           }
           umma_commit(&bar_empty[stage]);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -686,17 +701,20 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
       MBAR_WAIT_OR_TRAP(&bar_tfull, 0);
       tc_fence_after();
       const size_t co_stride = (size_t)p.co_stride;
-      const int q = p.convt ? n_tile / p.nt_per_q : 0;
-      const int co_base = p.convt ? q * p.Cout + (n_tile % p.nt_per_q) * p.block_n : n_tile * p.block_n;
-      const int co_lim = p.convt ? (q + 1) * p.Cout : p.Cout;
-      for (int mt = 0; mt < p.mt; ++mt) {
+      const int n_acc = p.quads == 4 ? 4 : p.mt;          // accumulators: quadrants (128 cols apart) or M tiles (256)
+      for (int acc = 0; acc < n_acc; ++acc) {
+        const int mt = p.quads == 4 ? 0 : acc;
+        const int q = !p.convt ? 0 : (p.quads == 4 ? acc : n_tile / p.nt_per_q);
+        const int nt = p.quads == 4 ? n_tile : n_tile % p.nt_per_q;
+        const int co_base = p.convt ? q * p.Cout + nt * p.block_n : n_tile * p.block_n;
+        const int co_lim = p.convt ? (q + 1) * p.Cout : p.Cout;
         int blk = (m_tile * p.mt + mt) * 2 + (row >> 6);
         const bool blk_ok = blk < p.m_blocks;
         if (!blk_ok) blk = p.m_blocks - 1;
         const int t = p.tap0 + blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
         const int ci = cc * 64 + (row & 63);
         const bool row_ok = blk_ok && ci < p.Cin;
-        const uint32_t t_addr = tmem_base + mt * 256 + (static_cast<uint32_t>(rb * 32) << 16);
+        const uint32_t t_addr = tmem_base + (p.quads == 4 ? acc * 128 : mt * 256) + (static_cast<uint32_t>(rb * 32) << 16);
         float* base = p.dw + (p.convt ? (size_t)0 : (size_t)t * p.Cin) + ci;
         for (int c0 = 0; c0 < p.block_n; c0 += 32) {
           uint32_t r[32];
@@ -1024,17 +1042,29 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   static int mt_env = -1;
   if (mt_env < 0) { const char* e = getenv("B200SEG_WGRAD_MT"); mt_env = (e != nullptr && e[0] == '1') ? 1 : 2; }
   p.mt = (mt_env == 2 && p.m_blocks >= 8) ? 2 : 1;
-  p.m_tiles = (p.m_blocks + 2 * p.mt - 1) / (2 * p.mt);
   p.block_n = Cout <= 256 ? Cout : (Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64));
+  // Transposed conv with few channels: 128-column tiles put all four output quadrants next to each other
+  // in TMEM, so one CTA serves them from ONE x tile (x was re-read once per quadrant and these layers are
+  // L2-bound).  For wide layers the dy re-reads of the extra M tiles would cost more than that saves.
+  // B200SEG_CONVT_QUADS=0 restores one quadrant per CTA.
+  static int quads_env = -1;
+  if (quads_env < 0) { const char* e = getenv("B200SEG_CONVT_QUADS"); quads_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  p.quads = 1;
+  if (convt && quads_env && Cout <= 256 && Cout % 64 == 0) {
+    p.quads = 4;
+    p.mt = 1;
+    p.block_n = Cout <= 128 ? Cout : 128;
+  }
+  p.m_tiles = (p.m_blocks + 2 * p.mt - 1) / (2 * p.mt);
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
   p.nt_per_q = (Cout + p.block_n - 1) / p.block_n;
-  p.n_tiles = (convt ? 4 : 1) * p.nt_per_q;
+  p.n_tiles = ((convt && p.quads == 1) ? 4 : 1) * p.nt_per_q;
   p.convt = convt;
   p.H = H;
   p.co_stride = convt ? Cin : (long long)9 * Cin;
   const int nblocks = (p.block_n + 63) / 64;
   p.a_bytes = 2 * p.mt * 8192;
-  p.b_bytes = nblocks * 8192;
+  p.b_bytes = p.quads * nblocks * 8192;
   p.stage_bytes = p.a_bytes + p.b_bytes;
   int stages = (int)(kSmemBudget / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;

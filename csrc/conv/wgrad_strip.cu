@@ -223,14 +223,26 @@ extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int 
   (void)N; (void)H;
   return (W >= 64 && Cin % 8 == 0 && Cout % 8 == 0) ? 1 : 0;
 }
-static int strip_bn(int Cout) {
-  static int force64 = -1;
-  if (force64 < 0) { const char* e = getenv("B200SEG_WGRAD_BN"); force64 = (e != nullptr && e[0] == '6') ? 1 : 0; }
-  return (!force64 && Cout % 128 == 0) ? 128 : 64;
+// 128-column variant: taps 0-7 at the full MMA rate, but tap (2,2) goes to the split-K kernel, which is
+// memory-bound for a single tap.  Measured per layer (profiles/conv_layers_*.txt) it pays when the rows
+// are long and the input is at least as wide as the output (W >= 128, Cin >= Cout); otherwise the
+// 64-column variant (all nine taps, five tiles) or, for Cout > 128, the split-K kernel is faster.
+// B200SEG_WGRAD_BN=64|128 forces one.
+static int strip_bn(int W, int Cin, int Cout) {
+  static int force = -1;
+  if (force < 0) {
+    const char* e = getenv("B200SEG_WGRAD_BN");
+    force = (e == nullptr) ? 0 : (e[0] == '6' ? 64 : 128);
+  }
+  if (Cout % 128 != 0 || force == 64) return 64;
+  if (force == 128) return 128;
+  return (W >= 128 && Cin >= Cout) ? 128 : 64;
 }
+// Wide outputs that do not qualify for the 128-column variant stay on the split-K kernel (256-column
+// tiles beat five 64-column ones there).
 extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout) {
   if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return 0;
-  return (Cout <= 128 || strip_bn(Cout) == 128) ? 1 : 0;
+  return (Cout <= 128 || strip_bn(W, Cin, Cout) == 128) ? 1 : 0;
 }
 
 extern "C" int b200conv_wgrad_taps(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
@@ -252,7 +264,7 @@ static int launch_strip(const CUtensorMap& mx, const CUtensorMap& mdy, const Wgr
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
                                     int N, int H, int W, int Cin, int Cout, cudaStream_t st) {
   if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return (int)cudaErrorInvalidValue;
-  const int bn = strip_bn(Cout);
+  const int bn = strip_bn(W, Cin, Cout);
   WgradStripParams p{};
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
   p.chunks = (Cin + 63) / 64;

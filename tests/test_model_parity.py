@@ -82,3 +82,28 @@ def test_wider_reference_variant(reference_script):
 def test_bad_upsample_mode():
     with pytest.raises(ValueError):
         UNet(up_sample_mode="nearest")
+
+
+def test_flat_layout_puts_tensor_core_weights_first():
+    """The flat buffer starts with the conv / convT weights whose gradients the wgrad kernels write
+    (the region the fused exchange reduces in their epilogues); everything small follows."""
+    from distributed_deep_learning_on_personal_computers_b200.models.unet import UNet
+    torch.manual_seed(0)
+    m = UNet(6, "conv_transpose", base_channels=16)
+    want = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    flat = m.flatten_parameters()
+    bulk, offs = flat["bulk_elems"], flat["offsets"]
+    assert 0 < bulk < flat["param"].numel() and bulk % 64 == 0
+    shapes = dict(m.named_parameters())
+    for name, (off, n) in offs.items():
+        p = shapes[name]
+        is_bulk = off < bulk
+        assert (off + n <= bulk) == is_bulk                       # no tensor straddles the boundary
+        if is_bulk:
+            assert p.dim() == 4 and p.shape[-1] > 1
+        else:
+            assert p.dim() == 1 or name.startswith("down_conv1.double_conv.double_conv.0") or "conv_last" in name
+    small = sum(n for _, (off, n) in offs.items() if off >= bulk)
+    assert small < 0.02 * bulk
+    for k, v in m.state_dict().items():                           # values and shapes survive the move
+        assert torch.equal(v, want[k])
