@@ -210,6 +210,20 @@ void conv3x3_dgrad(const Tensor& dy, const Tensor& w, Tensor dx) {
                     (int)dy.size(0), (int)dy.size(1), (int)dy.size(2), Cin, Cout, cur()), "conv3x3_dgrad");
 }
 
+Tensor conv3x3_dgrad_stats(const Tensor& dy, const Tensor& w, Tensor dx) {
+  c10::cuda::CUDAGuard g(dy.device());
+  bf16(dy, "dy"); bf16(w, "w"); bf16(dx, "dx");
+  const int Cout = (int)w.size(0), Cin = (int)w.size(3);
+  TORCH_CHECK(dx.size(3) == Cin && dy.size(3) == Cout, "channel mismatch");
+  const int N = (int)dy.size(0), H = (int)dy.size(1), W = (int)dy.size(2);
+  const int rows = b200conv_dgrad_stat_rows(N, H, W, Cin, Cout);
+  TORCH_CHECK(rows > 0, "conv3x3_dgrad_stats: unsupported shape");
+  Tensor part = at::empty({rows, 2, Cin}, dy.options().dtype(at::kFloat));
+  ok(b200conv_dgrad_stats(dy.data_ptr(), nhwc_ld(dy, "dy"), w.data_ptr(), dx.data_ptr(), nhwc_ld(dx, "dx"), N, H, W,
+                          Cin, Cout, part.data_ptr<float>(), cur()), "conv3x3_dgrad_stats");
+  return part;
+}
+
 void conv3x3_wgrad(const Tensor& x, const Tensor& dy, Tensor dw) {
   c10::cuda::CUDAGuard g(x.device());
   bf16(x, "x"); bf16(dy, "dy");
@@ -333,6 +347,7 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);
   m.def("conv3x3_dgrad(Tensor dy, Tensor w, Tensor(a!) dx) -> ()", &conv3x3_dgrad);
+  m.def("conv3x3_dgrad_stats(Tensor dy, Tensor w, Tensor(a!) dx) -> Tensor", &conv3x3_dgrad_stats);
   m.def("conv3x3_wgrad(Tensor x, Tensor dy, Tensor(a!) dw) -> ()", &conv3x3_wgrad);
   m.def("convT2x2_fwd(Tensor x, Tensor w, Tensor bias, Tensor(a!) out) -> ()", &convT2x2_fwd);
   m.def("convT2x2_bwd(Tensor x, Tensor d_up, Tensor w, Tensor(a!) dw, Tensor(b!)? dx) -> ()", &convT2x2_bwd);

@@ -405,13 +405,15 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     // swizzle<B,4,3>: chunk index XOR (row-derived constant); the XOR term only depends on the row
     const uint32_t my_row_off = row * row_bytes;
     const uint32_t my_rx = (my_row_off >> 7) & swz_mask;
-    // statistics: this thread owns ONE 16-byte chunk column (8 channels) of the N tile and walks
-    // st_rows of the 128 rows; requires block_n / 8 to divide 128 (power-of-two Cout).
+    // statistics: this thread owns ONE 16-byte chunk column (8 channels) of the N tile and walks every
+    // st_rstep-th of the 128 rows; when block_n / 8 does not divide the thread count (block_n = 192)
+    // the last few threads sit out.
     const int cpr = p.block_n >> 3;                       // chunks per row
     const int st_cc = et % cpr;                           // my chunk column
     const int st_rg = et / cpr;                           // my row group
     const int st_rstep = kEpiThreads / cpr;
-    const int st_rows = 128 / st_rstep;                   // rows of the tile this thread sums
+    const bool st_active = st_rg < st_rstep;
+    const int st_rows = st_active ? (128 - st_rg + st_rstep - 1) / st_rstep : 0;   // rows this thread sums
     const int st_grp = (st_cc * 8) >> ocb_log2;
     const uint32_t st_chunk = ((st_cc * 8) & (ocb - 1)) >> 3;
     float st_s[8], st_q[8];
@@ -539,10 +541,12 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       named_bar_sync(1, kEpiThreads);
       float* red = reinterpret_cast<float*>(staging0);   // [256/cpr][2][block_n]
       const int ncol = p.block_n;
+      if (st_active) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        red[(st_rg * 2 + 0) * ncol + st_cc * 8 + j] = st_s[j];
-        red[(st_rg * 2 + 1) * ncol + st_cc * 8 + j] = st_q[j];
+        for (int j = 0; j < 8; ++j) {
+          red[(st_rg * 2 + 0) * ncol + st_cc * 8 + j] = st_s[j];
+          red[(st_rg * 2 + 1) * ncol + st_cc * 8 + j] = st_q[j];
+        }
       }
       named_bar_sync(1, kEpiThreads);
       for (int c = et; c < ncol; c += kEpiThreads) {
@@ -869,7 +873,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if ((mode == 2 || mode == 3) && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.bias = bias;
   p.partials = partials;
-  if (partials != nullptr && (128 % (p.block_n / 8) != 0 || p.block_n < 16)) return (int)cudaErrorInvalidValue;
+  if (partials != nullptr && (p.block_n % 8 != 0 || p.block_n < 16 || p.block_n > 256)) return (int)cudaErrorInvalidValue;
   p.a_bytes = 128 * BK * 2;
   const bool bmn = (mode == 1 || mode == 3);
   const uint32_t b_raw = bmn ? (uint32_t)((p.block_n + 63) / 64) * 64 * BK * 2 : (uint32_t)p.block_n * BK * 2;
@@ -1016,6 +1020,20 @@ extern "C" int b200conv_fprop(const void* x, long long ld_x, const void* w, cons
 extern "C" int b200conv_dgrad(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
                               int H, int W, int Cin, int Cout, cudaStream_t st) {
   return run_tap_gemm(1, dy, ld_dy, w, nullptr, dx, ld_dx, N, H, W, Cout, Cin, Cin, nullptr, nullptr, false, st);
+}
+
+// dgrad that also returns per-CTA column sums of dx ([rows][2][Cin]: sum, sum of squares, of the
+// bf16-rounded output) -- the transposed conv's bias gradient is the column sum of the slice of dx it
+// reads, so this saves a separate pass over that tensor.
+extern "C" int b200conv_dgrad_stat_rows(int N, int H, int W, int Cin, int Cout) {
+  int rows = 0;
+  int e = run_tap_gemm(1, nullptr, Cout, nullptr, nullptr, nullptr, Cin, N, H, W, Cout, Cin, Cin, nullptr, &rows, true,
+                       0);
+  return e == 0 ? rows : 0;
+}
+extern "C" int b200conv_dgrad_stats(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
+                                    int H, int W, int Cin, int Cout, float* partials, cudaStream_t st) {
+  return run_tap_gemm(1, dy, ld_dy, w, nullptr, dx, ld_dx, N, H, W, Cout, Cin, Cin, partials, nullptr, false, st);
 }
 
 extern "C" int b200conv_convT_fwd(const void* x, long long ld_x, const void* w, const float* bias, void* out,

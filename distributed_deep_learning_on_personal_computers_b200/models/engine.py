@@ -192,7 +192,8 @@ class NativeEngine:
                        conv_bias=bias)
         Fn.bn_relu_pool_fwd(st.y, st.ss, st.out, st.pool)
 
-    def _stage_bwd(self, st: _Stage, need_dx: bool = True) -> None:
+    def _stage_bwd(self, st: _Stage, need_dx: bool = True, colsum: bool = False):
+        """``colsum``: also return the per-CTA column sums of ``dx`` from the dgrad epilogue."""
         sp = st.spec
         bn = sp.bn
         Fn.bn_relu_pool_bwd(st.d_out, st.d_pool if st.pool is not None else None, st.y, st.ss,
@@ -208,8 +209,11 @@ class NativeEngine:
         else:
             Fn.conv3x3_wgrad(st.x, st.dy, dw, impl=self.conv_impl)
         if need_dx and st.dx is not None:
-            Fn.conv3x3_dgrad(st.dy, self._w3(self.flat_lp, sp.name + ".weight"), st.dx,
-                             impl=self.conv_impl)
+            w_lp = self._w3(self.flat_lp, sp.name + ".weight")
+            if colsum:
+                return Fn.conv3x3_dgrad_stats(st.dy, w_lp, st.dx, impl=self.conv_impl)
+            Fn.conv3x3_dgrad(st.dy, w_lp, st.dx, impl=self.conv_impl)
+        return None
 
     # -- public steps --------------------------------------------------------------------------------
     @torch.no_grad()
@@ -263,7 +267,9 @@ class NativeEngine:
         for i in (1, 2, 3, 4, 5):
             s0, s1 = self.stages[f"up_conv{i}"]
             self._stage_bwd(s1)
-            self._stage_bwd(s0)
+            # the up-sampled slice of d_cat is written by this dgrad; its column sums are the transposed
+            # conv's bias gradient
+            part = self._stage_bwd(s0, colsum=not self.bilinear)
             below, d_below = self.up_io[i]
             d_up = self.d_cat[i][..., :self.c_up[i]]
             if self.bilinear:
@@ -272,7 +278,7 @@ class NativeEngine:
                 name = f"up_conv{i}.up_sample"
                 Fn.convT2x2_bwd(below, d_up, self._params[name + ".weight"], self._convT_lp(name),
                                 self._params[name + ".weight"].grad,
-                                self._seg(self.flat_g, name + ".bias"), d_below)
+                                self._seg(self.flat_g, name + ".bias"), d_below, d_up_partials=part)
         s0, s1 = self.stages["double_conv"]
         self._stage_bwd(s1)
         self._stage_bwd(s0)

@@ -108,6 +108,18 @@ def conv3x3_dgrad(dy, w, dx, impl=None):
     return ref.conv3x3_dgrad(dy, w, dx)
 
 
+def conv3x3_dgrad_stats(dy, w, dx, impl=None):
+    """``conv3x3_dgrad`` that also returns per-CTA column sums of ``dx`` (``[rows, 2, Cin]``: sum and sum
+    of squares) from the kernel's epilogue, or ``None`` where that kernel is not in use.  The transposed
+    conv's bias gradient is such a column sum (``convT2x2_bwd(..., d_up_partials=...)``)."""
+    if _native(dy) and _use_tc(w.shape[3], w.shape[0], impl):
+        part = _ops().conv3x3_dgrad_stats(dy, w, dx)
+        _tick()
+        return part
+    conv3x3_dgrad(dy, w, dx, impl=impl)
+    return None
+
+
 def conv3x3_wgrad(x, dy, dw, impl=None):
     if _native(x):
         cout, _, _, cin = dw.shape
@@ -168,7 +180,7 @@ def convT2x2_fwd(x, w_param, w_lp, bias, out, impl=None):
     ref.convT2x2_fwd(x, w_param, bias, out)
 
 
-def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx, impl=None):
+def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx, impl=None, d_up_partials=None):
     """Backward of the transposed conv.  Data gradient = a stride-2 2x2 conv of d_up (a tap GEMM over
     the four quadrants, gathered by a 5-D TMA box); weight gradient = the wgrad kernel with the
     quadrant as the N tile.  ``dw_param`` is the logical (Cin,Cout,2,2) view of the flat gradient."""
@@ -176,11 +188,15 @@ def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx, impl=None):
         cout4, cin = w_lp.shape
         cout = cout4 // 4
         if _use_tc(cin, cout, impl):
-            part = torch.empty(_ops().stats_rows(), 2, cout, dtype=torch.float32, device=x.device)
-            _ops().channel_stats(d_up, part)
-            dbias.add_(part[:, 0, :].sum(0))
+            if d_up_partials is not None:        # column sums of d_up already came out of the dgrad that wrote it
+                dbias.add_(d_up_partials[:, 0, :cout].sum(0))
+                _tick(2)
+            else:
+                part = torch.empty(_ops().stats_rows(), 2, cout, dtype=torch.float32, device=x.device)
+                _ops().channel_stats(d_up, part)
+                dbias.add_(part[:, 0, :].sum(0))
+                _tick(3)
             _ops().convT2x2_bwd(x, d_up, w_lp, _flat_of(dw_param).reshape(4 * cout, cin), dx)
-            _tick(3)
             return
         wl = w_lp.view(2, 2, cout, cin).permute(3, 2, 0, 1)               # logical (Cin,Cout,2,2)
         g = d_up.permute(0, 3, 1, 2)

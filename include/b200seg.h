@@ -110,6 +110,10 @@ int b200conv_fprop(const void* x, long long ld_x, const void* w, const float* bi
                    cudaStream_t st);
 int b200conv_dgrad(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
                    int H, int W, int Cin, int Cout, cudaStream_t st);
+/* dgrad + per-CTA column sums of dx: partials = float[rows][2][Cin], rows = b200conv_dgrad_stat_rows(...) */
+int b200conv_dgrad_stat_rows(int N, int H, int W, int Cin, int Cout);
+int b200conv_dgrad_stats(const void* dy, long long ld_dy, const void* w, void* dx, long long ld_dx, int N,
+                         int H, int W, int Cin, int Cout, float* partials, cudaStream_t st);
 int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
                    int H, int W, int Cin, int Cout, cudaStream_t st);
 /* the same for filter taps tap0 .. tap0+ntaps-1 only (tap = 3*r + s), split-K kernel */

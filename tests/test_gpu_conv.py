@@ -62,6 +62,12 @@ def test_conv3x3_dgrad(shape):
     dx_ref = ref.conv3x3_dgrad(dy.float(), w.float())
     torch.testing.assert_close(dx.float(), dx_ref, rtol=2e-2, atol=3e-2)
     assert (wide[..., :32] == 0).all()
+    # same kernel with column sums of dx from the epilogue (the transposed conv's bias gradient)
+    dx2 = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device=DEV)
+    part = Fn.conv3x3_dgrad_stats(dy, w, dx2, impl="tcgen05")
+    assert torch.equal(dx2, dx.contiguous())
+    want = torch.stack([dx2.float().sum((0, 1, 2)), (dx2.float() ** 2).sum((0, 1, 2))])
+    torch.testing.assert_close(part.sum(0), want, rtol=1e-3, atol=1e-1)
 
 
 @pytest.mark.parametrize("shape", SHAPES)
