@@ -140,7 +140,7 @@ def _fused_worker(rank, world, port, q, out_dir):
     from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
     from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
     from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
-    cfg = TrainConfig(base_channels=32, tile=128, train_tiles=8, holdout_tiles=0, batch_size=2, sync_every=1,
+    cfg = TrainConfig(base_channels=32, tile=128, train_tiles=4 * world, holdout_tiles=0, batch_size=2, sync_every=1,
                       epochs=1, codec="fp32", comm="fused", device="cuda", out_dir=out_dir, sample_images=0,
                       cuda_graph=False, timeout_s=120).apply_env()
     tr = Trainer(cfg)
