@@ -111,7 +111,10 @@ class RankSampler:
 
 
 class PinnedBatchLoader:
-    """Ring of pinned host buffers + a copy stream: batch k+1 is in flight while k computes."""
+    """Ring of pinned host buffers + a copy stream + one staging thread: while batch k computes, the
+    thread gathers batch k+1, k+2 into pinned memory and queues their host-to-device copies, so neither
+    the host gather nor the PCIe transfer sits between two steps (the reference slices and ``.cuda()``s
+    every micro-batch synchronously, R:754-755)."""
 
     def __init__(self, tiles: TileSet, batch: int, device: torch.device, depth: int = 3):
         self.tiles, self.batch, self.device = tiles, batch, device
@@ -128,11 +131,14 @@ class PinnedBatchLoader:
         self.consumed = [torch.cuda.Event() for _ in range(depth)] if self.cuda else None
         self.bytes_per_batch = batch * h * w * (c + 1)
         self._used = [False] * depth
+        self._pool = None
 
     def _stage(self, slot: int, idx: List[int]) -> None:
         sel = torch.as_tensor(idx, dtype=torch.long)
-        if self.cuda and self._used[slot]:
-            self.consumed[slot].synchronize()        # host buffer / device slot free again
+        if self.cuda:
+            torch.cuda.set_device(self.device)       # may run on the staging thread
+            if self._used[slot]:
+                self.consumed[slot].synchronize()    # host buffer / device slot free again
         torch.index_select(self.tiles.images, 0, sel, out=self.h_img[slot])
         torch.index_select(self.tiles.labels, 0, sel, out=self.h_lab[slot])
         if self.cuda:
@@ -145,14 +151,27 @@ class PinnedBatchLoader:
             self.d_lab[slot].copy_(self.h_lab[slot])
         self._used[slot] = True
 
+    def _submit(self, slot: int, idx: List[int]):
+        if not self.cuda:
+            self._stage(slot, idx)
+            return None
+        if self._pool is None:
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="b200seg-stage")
+        return self._pool.submit(self._stage, slot, idx)
+
     def batches(self, order: List[int]) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
         """Yields device uint8 ``(images NHWC, labels NHW)``; drops a ragged tail batch."""
         groups = [order[i:i + self.batch] for i in range(0, len(order) - self.batch + 1, self.batch)]
         ahead = min(self.depth - 1, len(groups))
+        pending = {}
         for k in range(ahead):
-            self._stage(k % self.depth, groups[k])
+            pending[k] = self._submit(k % self.depth, groups[k])
         for k in range(len(groups)):
             slot = k % self.depth
+            fut = pending.pop(k, None)
+            if fut is not None:
+                fut.result()                              # the copy is queued and `ready` recorded
             if self.cuda:
                 torch.cuda.current_stream(self.device).wait_event(self.ready[slot])
             yield self.d_img[slot], self.d_lab[slot]
@@ -160,7 +179,10 @@ class PinnedBatchLoader:
                 self.consumed[slot].record(torch.cuda.current_stream(self.device))
             nxt = k + ahead
             if nxt < len(groups):
-                self._stage(nxt % self.depth, groups[nxt])
+                pending[nxt] = self._submit(nxt % self.depth, groups[nxt])
+        for fut in pending.values():
+            if fut is not None:
+                fut.result()
 
 
 def build_datasets(cfg) -> Tuple[TileSet, Optional[TileSet]]:
