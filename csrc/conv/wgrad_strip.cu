@@ -50,11 +50,31 @@ template <int BN> struct WsCfg {
 struct WgradStripParams {
   int N, H, W, Cin, Cout;
   int chunks, n_tiles, groups;         // Cin/64 (rounded up), Cout/BN (rounded up), chunks * n_tiles
-  int ctas_per_group;
   int wsegs, rows_per_piece, pieces_per_col, pieces;   // pieces per group
   float* dw;
   long long mc_delta;                  // != 0: add through the multicast alias (fused all-reduce)
 };
+
+// Work distribution ("stream-K" over pixels): the (group, piece) pairs -- group = (Cin chunk, Cout tile),
+// piece = rows_per_piece rows of one 64-pixel column -- are numbered group-major and the grid's CTAs
+// take equal contiguous ranges.  A CTA therefore usually works for one group, sometimes two or three;
+// at a group boundary it flushes its accumulators (epilogue) and starts over.  Vertically adjacent
+// pieces of a range are walked as ONE span, so the two halo rows are paid once per span, not per piece.
+struct WsSpan { int group, n, w0, h0, h1, next; };
+__device__ __forceinline__ WsSpan ws_span(const WgradStripParams& p, int gid, int g1) {
+  WsSpan s;
+  s.group = gid / p.pieces;
+  const int piece = gid - s.group * p.pieces;
+  const int col = piece / p.pieces_per_col, seg = piece - col * p.pieces_per_col;
+  int nseg = p.pieces_per_col - seg;
+  if (gid + nseg > g1) nseg = g1 - gid;
+  s.n = col / p.wsegs;
+  s.w0 = (col - s.n * p.wsegs) * 64;
+  s.h0 = seg * p.rows_per_piece;
+  s.h1 = min(p.H, (seg + nseg) * p.rows_per_piece);
+  s.next = gid + nseg;
+  return s;
+}
 
 template <int BN>
 __global__ void __launch_bounds__(kWsThreads, 1)
@@ -63,22 +83,22 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ __align__(8) uint64_t bar_full[kWsStages], bar_empty[kWsStages];
-  __shared__ __align__(8) uint64_t bar_done;
+  __shared__ __align__(8) uint64_t bar_done, bar_drained;
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kDyBytes = WsCfg<BN>::kDyBytes, kWsStageBytes = WsCfg<BN>::kStageBytes;
   constexpr int kTiles = WsCfg<BN>::kTiles;
 
-  const int group = blockIdx.x % p.groups;
-  const int member = blockIdx.x / p.groups;              // which CTA of the group
-  const int chunk = group % p.chunks;
-  const int n_tile = group / p.chunks;
+  const long long total = (long long)p.groups * p.pieces;
+  const int g0 = (int)(total * blockIdx.x / gridDim.x);
+  const int g1 = (int)(total * (blockIdx.x + 1) / gridDim.x);
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_dy);
     for (int s = 0; s < kWsStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
     mbar_init(&bar_done, 1);
+    mbar_init(&bar_drained, 128);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
@@ -88,20 +108,19 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   pdl_wait();
   pdl_trigger();
   const uint32_t tmem_base = tmem_base_s;
-  const bool has_work = member < p.pieces;
+  const bool has_work = g1 > g0;
 
   if (warp == 0) {
     // ------------------------------------------------ producer ------------------------------------
     if (elect_one() && has_work) {
       uint32_t q = 0;                                      // global stage counter
-      for (int piece = member; piece < p.pieces; piece += p.ctas_per_group) {
-        const int col = piece / p.pieces_per_col, seg = piece % p.pieces_per_col;
-        const int n = col / p.wsegs, w0 = (col % p.wsegs) * 64;
-        const int h0 = seg * p.rows_per_piece;
-        const int h1 = min(p.H, h0 + p.rows_per_piece);
-        // stage j of the piece carries input row (h0 - 1 + j); from j = 2 on it also carries the dy
+      for (int gid = g0; gid < g1;) {
+        const WsSpan sp = ws_span(p, gid, g1);
+        gid = sp.next;
+        const int chunk = sp.group % p.chunks, n_tile = sp.group / p.chunks;
+        // stage j of the span carries input row (h0 - 1 + j); from j = 2 on it also carries the dy
         // tile of output row (h0 + j - 2).
-        const int nst = (h1 - h0) + 2;
+        const int nst = (sp.h1 - sp.h0) + 2;
         for (int j = 0; j < nst; ++j, ++q) {
           const int st = q % kWsStages;
           MBAR_WAIT_OR_TRAP(&bar_empty[st], ((q / kWsStages) & 1) ^ 1);
@@ -109,15 +128,15 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           const bool with_dy = j >= 2;
           const bool mirror = st == 0;                     // slot 0 is duplicated behind the last slot
           mbar_arrive_expect_tx(&bar_full[st], (mirror ? 2 : 1) * 66 * 128 + (with_dy ? kDyBytes : 0));
-          tma_load_4d(sx, &map_x, &bar_full[st], chunk * 64, w0 - 1, h0 - 1 + j, n);
+          tma_load_4d(sx, &map_x, &bar_full[st], chunk * 64, sp.w0 - 1, sp.h0 - 1 + j, sp.n);
           if (mirror)
-            tma_load_4d(smem + (size_t)kWsStages * kWsStageBytes, &map_x, &bar_full[st], chunk * 64, w0 - 1,
-                        h0 - 1 + j, n);
+            tma_load_4d(smem + (size_t)kWsStages * kWsStageBytes, &map_x, &bar_full[st], chunk * 64, sp.w0 - 1,
+                        sp.h0 - 1 + j, sp.n);
           if (with_dy) {
 #pragma unroll
             for (int nb = 0; nb < BN / 64; ++nb)
-              tma_load_4d(sx + kStripBytes + nb * 8192, &map_dy, &bar_full[st], n_tile * BN + nb * 64, w0,
-                          h0 + j - 2, n);
+              tma_load_4d(sx + kStripBytes + nb * 8192, &map_dy, &bar_full[st], n_tile * BN + nb * 64, sp.w0,
+                          sp.h0 + j - 2, sp.n);
           }
         }
       }
@@ -129,15 +148,24 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       const uint32_t sbase = smem_u32(smem);
       uint32_t q = 0;
       bool first = true;
-      for (int piece = member; piece < p.pieces; piece += p.ctas_per_group) {
-        const int seg = piece % p.pieces_per_col;
-        const int h0 = seg * p.rows_per_piece;
-        const int h1 = min(p.H, h0 + p.rows_per_piece);
-        const int nst = (h1 - h0) + 2;
+      int cur_group = g0 / p.pieces;
+      uint32_t seg_no = 0;
+      for (int gid = g0; gid < g1;) {
+        const WsSpan sp = ws_span(p, gid, g1);
+        gid = sp.next;
+        if (sp.group != cur_group) {                        // group boundary: hand the accumulators over
+          umma_commit(&bar_done);
+          MBAR_WAIT_OR_TRAP(&bar_drained, seg_no & 1);      // ... and wait until they have been read out
+          tc_fence_after();
+          ++seg_no;
+          cur_group = sp.group;
+          first = true;
+        }
+        const int nst = (sp.h1 - sp.h0) + 2;
         for (int j = 0; j < nst; ++j, ++q) {
           const int st = q % kWsStages;
           MBAR_WAIT_OR_TRAP(&bar_full[st], (q / kWsStages) & 1);
-          if (j < 2) continue;                              // halo rows of the piece: loaded only
+          if (j < 2) continue;                              // halo rows of the span: loaded only
           tc_fence_after();
           const uint32_t strip0 = sbase + ((q - 2) % kWsStages) * kWsStageBytes;   // filter row 0
           const uint32_t strip1 = sbase + ((q - 1) % kWsStages) * kWsStageBytes;
@@ -157,7 +185,7 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           }
           first = false;
           umma_commit(&bar_empty[(q - 2) % kWsStages]);    // oldest strip is no longer needed
-          if (j == nst - 1) {                               // end of the piece: free the other two
+          if (j == nst - 1) {                               // end of the span: free the other two
             umma_commit(&bar_empty[(q - 1) % kWsStages]);
             umma_commit(&bar_empty[st]);
           }
@@ -166,45 +194,53 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       umma_commit(&bar_done);
     }
   } else if (has_work) {
-    // ------------------------------------------------ epilogue (once) -----------------------------
+    // ------------------------------------------------ epilogue (once per group touched) -----------
     const int rb = warp & 3;
     const int row = rb * 32 + lane;                         // accumulator row: tap half + channel
-    const int ci = chunk * 64 + (row & 63);
-    MBAR_WAIT_OR_TRAP(&bar_done, 0);
-    tc_fence_after();
     const size_t co_stride = (size_t)9 * p.Cin;
+    const int grp_first = g0 / p.pieces, grp_last = (g1 - 1) / p.pieces;
+    uint32_t seg_no = 0;
+    for (int group = grp_first; group <= grp_last; ++group, ++seg_no) {
+      const int chunk = group % p.chunks, n_tile = group / p.chunks;
+      const int ci = chunk * 64 + (row & 63);
+      MBAR_WAIT_OR_TRAP(&bar_done, seg_no & 1);
+      tc_fence_after();
 #pragma unroll 1
-    for (int t = 0; t < kTiles; ++t) {
-      const int hi = row >> 6;                              // which tap of the tile (warp-uniform)
-      const int r = t < 3 ? t : (t == 3 ? hi : 2);
-      const int s = t < 3 ? hi : 2;
-      if (t == 4 && hi) continue;                           // padding half of the last tile
-      const bool row_ok = ci < p.Cin;
-      float* base = p.dw + (size_t)(r * 3 + s) * p.Cin + ci;
-      const uint32_t t_addr = tmem_base + t * BN + (static_cast<uint32_t>(rb * 32) << 16);
+      for (int t = 0; t < kTiles; ++t) {
+        const int hi = row >> 6;                            // which tap of the tile (warp-uniform)
+        const int r = t < 3 ? t : (t == 3 ? hi : 2);
+        const int s = t < 3 ? hi : 2;
+        if (t == 4 && hi) continue;                         // padding half of the last tile
+        const bool row_ok = ci < p.Cin;
+        float* base = p.dw + (size_t)(r * 3 + s) * p.Cin + ci;
+        const uint32_t t_addr = tmem_base + t * BN + (static_cast<uint32_t>(rb * 32) << 16);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(t_addr + c0, v);
-        tmem_ld_wait();
-        if (p.mc_delta != 0) {                                // fused all-reduce: 16-byte multicast reductions
-          quad_transpose32(v, lane);
-          float* qbase = base - (lane & 3);                   // first of the quad's four channels
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_addr + c0, v);
+          tmem_ld_wait();
+          if (p.mc_delta != 0) {                            // fused all-reduce: 16-byte multicast reductions
+            quad_transpose32(v, lane);
+            float* qbase = base - (lane & 3);               // first of the quad's four channels
 #pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const int co = n_tile * BN + c0 + 4 * g + (lane & 3);
-            if (row_ok && co < p.Cout)
-              grad_red_add4_mc(qbase + (size_t)co * co_stride, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
-                               __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]), p.mc_delta);
+            for (int g = 0; g < 8; ++g) {
+              const int co = n_tile * BN + c0 + 4 * g + (lane & 3);
+              if (row_ok && co < p.Cout)
+                grad_red_add4_mc(qbase + (size_t)co * co_stride, __uint_as_float(v[4 * g]),
+                                 __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                                 __uint_as_float(v[4 * g + 3]), p.mc_delta);
+            }
+            continue;
           }
-          continue;
-        }
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int co = n_tile * BN + c0 + j;
-          if (row_ok && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(v[j]));
+          for (int j = 0; j < 32; ++j) {
+            const int co = n_tile * BN + c0 + j;
+            if (row_ok && co < p.Cout) atomicAdd(base + (size_t)co * co_stride, __uint_as_float(v[j]));
+          }
         }
       }
+      tc_fence_before();
+      mbar_arrive(&bar_drained);                            // the MMA thread may overwrite the accumulators
     }
   }
   tc_fence_before();
@@ -271,13 +307,12 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
   p.n_tiles = (Cout + bn - 1) / bn;
   p.groups = p.chunks * p.n_tiles;
   p.wsegs = (W + 63) / 64;
-  p.rows_per_piece = H < 32 ? H : 32;
+  p.rows_per_piece = H < 8 ? H : 8;                      // granularity of the split between CTAs only
   p.pieces_per_col = (H + p.rows_per_piece - 1) / p.rows_per_piece;
   p.pieces = N * p.wsegs * p.pieces_per_col;
-  int cpg = kNumSMs / p.groups;
-  if (cpg < 1) cpg = 1;
-  if (cpg > p.pieces) cpg = p.pieces;
-  p.ctas_per_group = cpg;
+  const long long total = (long long)p.groups * p.pieces;
+  if (total > 0x7fffffffll) return (int)cudaErrorInvalidValue;
+  const int grid = total < kNumSMs ? (int)total : kNumSMs;
   p.dw = dw;
   p.mc_delta = b200seg_grad_multicast_delta(dw);
   CUtensorMap mx, mdy;
@@ -291,8 +326,8 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
     int box[4] = {64, 64, 1, 1};
     if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   }
-  if (bn == 64) return launch_strip<64>(mx, mdy, p, p.groups * cpg, st);
-  int rc = launch_strip<128>(mx, mdy, p, p.groups * cpg, st);
+  if (bn == 64) return launch_strip<64>(mx, mdy, p, grid, st);
+  int rc = launch_strip<128>(mx, mdy, p, grid, st);
   if (rc != 0) return rc;
   return b200conv_wgrad_taps(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, 8, 1, st);   // tap (2,2)
 }
