@@ -63,6 +63,7 @@ struct TapGemmParams {
   int staging_bufs;                // 1 or 2 output staging tiles (2: TMA store of tile i overlaps tile i+1)
   int cluster;                     // 1, or 2: CTA pairs (adjacent M tiles) share the weight tile via TMA multicast
   int rows2;                       // STRIP mode: a work unit is TWO vertically adjacent row tiles sharing every weight tile
+  int rows4;                       // STRIP mode, resident bank, N = 64: FOUR-row units, vertical taps merged along N
   int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
   int xslots;                      // STRIP mode: number of input-strip slots
   uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
@@ -176,10 +177,31 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       if (p.b_resident) {                                   // the whole filter bank, once
         mbar_arrive_expect_tx(&bar_full[0], 9 * p.kc_per_tap * p.b_bytes);
         for (int t = 0; t < 9; ++t)
-          for (int kc = 0; kc < p.kc_per_tap; ++kc)
-            load_b(smem + (size_t)(t * p.kc_per_tap + kc) * p.stage_bytes, &bar_full[0], t, kc);
+          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
+            // rows4: the three filter rows of one horizontal tap sit next to each other, in the order
+            // in which their output rows ascend (fprop: r = 2,1,0; dgrad: r = 0,1,2), so that a stack
+            // of them is ONE N = 128 / 192 operand
+            const int r = t / 3, sft = t % 3;
+            const int slot = p.rows4 ? (sft * 3 + (p.flip > 0 ? 2 - r : r)) : (t * p.kc_per_tap + kc);
+            load_b(smem + (size_t)slot * p.stage_bytes, &bar_full[0], t, kc);
+          }
       }
-      if (p.rows2) {
+      if (p.rows4) {
+        // work unit = output rows h0 .. h0+3 of one 128-pixel column segment: six input strips
+        const int hq_n = p.H >> 2;
+        for (int q = m_first; q < (p.m_tiles >> 2); q += m_step) {
+          const int twi = q % p.tiles_w;
+          const int hq = (q / p.tiles_w) % hq_n;
+          const int n0 = q / (p.tiles_w * hq_n);
+          const int w0 = twi << p.tw_log2, h0 = hq * 4;
+          for (int j = 0; j < 6; ++j) {
+            MBAR_WAIT_OR_TRAP(&bar_xempty[xs], xphase ^ 1);
+            mbar_arrive_expect_tx(&bar_xfull[xs], 130 * KCfg<BLOCK_K>::kRowBytes);
+            tma_load_4d(xring + (size_t)xs * p.xslot_bytes, &map_a, &bar_xfull[xs], 0, w0 - 1, h0 - 1 + j, n0);
+            if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+          }
+        }
+      } else if (p.rows2) {
         // work unit = output rows (h0, h0+1) of one 128-pixel column segment: 4 input strips per K chunk
         // (rows h0-1 .. h0+2) and every weight tile ONCE for both rows
         const int hp_n = p.H >> 1;
@@ -263,7 +285,63 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       int acc = 0;
       uint32_t acc_phase = 0;
       if (p.b_resident) MBAR_WAIT_OR_TRAP(&bar_full[0], 0);
-      if (p.rows2) {
+      if (p.rows4) {
+        // Four output rows per unit, 64 columns each, side by side in one 256-column accumulator.  Input
+        // strip j (image row h0-1+j) feeds output rows j-2 .. j through the three filter rows; because the
+        // weights of those filter rows are adjacent in shared memory, ONE instruction with N = 128 / 192
+        // does all of them: the activation window (the operand that made N = 64 shared-memory-bound) is
+        // read once per 2-3 output rows.  The row that a strip touches first (row j, filter row 0 in
+        // fprop) needs accumulate = 0, so the first horizontal tap issues it separately.
+        const uint32_t idesc_n[4] = {0u, make_idesc_bf16(128, 64, 0, B_MN ? 1 : 0), make_idesc_bf16(128, 128, 0, B_MN ? 1 : 0),
+                                     make_idesc_bf16(128, 192, 0, B_MN ? 1 : 0)};
+        for (int q = m_first; q < (p.m_tiles >> 2); q += m_step) {
+          MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d0 = tmem_base + acc * 256;
+#pragma unroll
+          for (int j = 0; j < 6; ++j) {
+            MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
+            tc_fence_after();
+            const uint64_t da_strip = make_smem_desc(smem_u32(xring + (size_t)xs * p.xslot_bytes), 16,
+                                                     KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+            const int sub_min = j > 2 ? j - 2 : 0, sub_max = j < 3 ? j : 3;
+            const int nb = sub_max - sub_min + 1;
+            const int first_blk = j < 2 ? 2 - j : 0;
+            const bool has_new = j <= 3;                   // output row j gets its first contribution here
+#pragma unroll
+            for (int sft = 0; sft < 3; ++sft) {
+              const int win = (p.flip > 0) ? sft : 2 - sft;
+              const uint64_t da0 = da_strip + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
+              const uint32_t sb = smem_u32(smem + (size_t)(sft * 3 + first_blk) * p.stage_bytes);
+              const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
+                                        : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+              if (sft == 0 && has_new) {
+                const int nb_old = nb - 1;
+                if (nb_old > 0) {
+#pragma unroll
+                  for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
+                    umma_bf16(d0 + sub_min * 64, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
+                              idesc_n[nb_old], 1u);
+                }
+                const uint64_t dbn = db0 + ((nb_old * p.stage_bytes) >> 4);
+#pragma unroll
+                for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
+                  umma_bf16(d0 + j * 64, da0 + ((k4 * 32) >> 4), dbn + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
+                            idesc_n[1], k4 == 0 ? 0u : 1u);
+              } else {
+#pragma unroll
+                for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
+                  umma_bf16(d0 + sub_min * 64, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
+                            idesc_n[nb], 1u);
+              }
+            }
+            umma_commit(&bar_xempty[xs]);
+            if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+          }
+          umma_commit(&bar_tfull[acc]);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+      } else if (p.rows2) {
         for (int q = m_first; q < (p.m_tiles >> 1); q += m_step) {
           // accumulator slots acc, acc+1 (of 4, 128 columns each) hold output rows h0 and h0+1
           MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
@@ -429,16 +507,20 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint8_t* const staging0 = staging;
     const int acc_n = p.rows2 ? 4 : 2;                    // accumulator slots in TMEM ...
     const int acc_cols = p.rows2 ? 128 : 256;             // ... and their column pitch
-    const int subs = p.rows2 ? 2 : 1;
-    const int n_units = p.rows2 ? (p.m_tiles >> 1) : m_units;
+    const int subs = p.rows4 ? 4 : (p.rows2 ? 2 : 1);     // output rows (tiles) per work unit
+    const int n_units = p.rows4 ? (p.m_tiles >> 2) : (p.rows2 ? (p.m_tiles >> 1) : m_units);
     for (int mu = m_first; mu < n_units; mu += m_step)
     for (int sub = 0; sub < subs; ++sub) {
-      const bool live = p.rows2 ? true : (mu * csz + crank < p.m_tiles);
+      const bool live = (p.rows2 | p.rows4) ? true : (mu * csz + crank < p.m_tiles);
       uint8_t* const staging = staging0 + (size_t)sbuf * p.staging_bytes;     // this tile's staging buffer
       if (p.staging_bufs == 2) sbuf ^= 1;
-      MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t t_addr = tmem_base + acc * acc_cols + (static_cast<uint32_t>(rb * 32) << 16);
+      // rows4: the unit's four rows share ONE accumulator slot (64 columns each)
+      if (!p.rows4 || sub == 0) {
+        MBAR_WAIT_OR_TRAP(&bar_tfull[acc], acc_phase);
+        tc_fence_after();
+      }
+      const uint32_t t_addr = tmem_base + acc * acc_cols + (p.rows4 ? sub * 64 : 0) +
+                              (static_cast<uint32_t>(rb * 32) << 16);
       for (int c0 = colhalf * 32; c0 < block_n; c0 += 64) {
         uint32_t r[32];
         const bool wide = block_n - c0 >= 32;
@@ -472,16 +554,19 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
       }
       tc_fence_before();
-      mbar_arrive(&bar_tempty[acc]);                      // accumulator drained: MMA may reuse it
-      if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
+      if (!p.rows4 || sub == 3) {
+        mbar_arrive(&bar_tempty[acc]);                    // accumulator drained: MMA may reuse it
+        if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
+      }
       fence_proxy_async();                                // staging writes -> visible to TMA
       named_bar_sync(1, kEpiThreads);
       int w0 = 0, h0 = 0, n0 = 0;
       if (et == 0 || (ragged && want_stats)) {            // tile coordinates: integer divisions, off the hot path
-        if (p.rows2) {
-          const int hp_n = p.H >> 1;
+        if (p.rows2 | p.rows4) {
+          const int sh = p.rows4 ? 2 : 1;
+          const int hp_n = p.H >> sh;
           w0 = (mu % p.tiles_w) << p.tw_log2;
-          h0 = ((mu / p.tiles_w) % hp_n) * 2 + sub;
+          h0 = (((mu / p.tiles_w) % hp_n) << sh) + sub;
           n0 = mu / (p.tiles_w * hp_n);
         } else {
           const int m = min(mu * csz + crank, p.m_tiles - 1);
@@ -825,6 +910,12 @@ static int cluster_env() {             // B200SEG_CLUSTER=1 enables CTA-pair wei
   return v;
 }
 
+static int rows4_env() {               // four-row N-merged units (N = 64, resident bank): 0 off, 1 dgrad only (default), 2 also fprop
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("B200SEG_ROWS4"); v = (e == nullptr) ? 1 : (e[0] == '0' ? 0 : (e[0] == '2' ? 2 : 1)); }
+  return v;
+}
+
 static int rows2_env() {               // B200SEG_ROWS2=0 disables the two-row strip work units
   static int v = -1;
   if (v < 0) { const char* e = getenv("B200SEG_ROWS2"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
@@ -897,6 +988,15 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.rows2 = (!p.b_resident && rows2_env() && (H % 2 == 0) && p.block_n <= 128 &&
                fits(1, 8, 3)) ? 1 : 0;
     if (p.rows2) p.staging_bufs = fits(2, 8, 6) ? 2 : 1;
+    // four-row units with the vertical taps merged along N (resident bank, N = 64, one K chunk): the
+    // bank's tiles must be exactly one 64-row block each so that stacked filter rows are contiguous.
+    // Measured (profiles/variants_in_situ.txt): dgrad 64->64 0.385 -> 0.326 ms; fprop unchanged (its
+    // epilogue with the BN statistics is the bound, not the MMAs), so fprop keeps the simpler units
+    // unless B200SEG_ROWS4=2.
+    p.rows4 = (p.b_resident && (rows4_env() == 2 || (rows4_env() == 1 && mode == 1)) && (H % 4 == 0) &&
+               p.block_n == 64 && p.n_total == 64 &&
+               p.kc_per_tap == 1 && p.stage_bytes == 64u * BK * 2u && fits(1, 6, 0)) ? 1 : 0;
+    if (p.rows4) p.staging_bufs = fits(2, 6, 0) ? 2 : 1;
     if (!fits(p.staging_bufs, 4, 3)) {
       strip = false;
     } else {
@@ -904,7 +1004,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
       while (!fits(p.staging_bufs, 4, bst)) --bst;         // weight ring: 6 deep if possible, never < 3
       // every tile needs 3 strips per K chunk and a TMA round trip is ~1.5 us: give the strip ring as
       // many slots as shared memory allows
-      int xs = p.rows2 ? 8 : 4;
+      int xs = p.rows2 ? 8 : (p.rows4 ? 6 : 4);
       while (!fits(p.staging_bufs, xs, bst) && bst > 3) --bst;
       while (xs < kMaxXSlots && fits(p.staging_bufs, xs + 1, bst)) ++xs;
       if (p.rows2) xs -= xs % 4;                            // a K chunk's four strips never straddle the ring end
@@ -916,7 +1016,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.tiles_w = g.tiles_w; p.tiles_h = g.tiles_h; p.tiles_g = g.tiles_g;
     p.m_tiles = g.tiles_w * g.tiles_h * g.tiles_g;
     p.tw_log2 = g.tw_log2; p.th_log2 = g.th_log2; p.tn = g.tn;
-    p.xslots = 0; p.xslot_bytes = 0; p.rows2 = 0; p.b_resident = 0;
+    p.xslots = 0; p.xslot_bytes = 0; p.rows2 = 0; p.rows4 = 0; p.b_resident = 0;
     p.stage_bytes = p.a_bytes + ((b_raw + 1023) / 1024) * 1024;
     p.staging_bufs = (2 * p.staging_bytes + 4 * p.stage_bytes <= kSmemBudget) ? 2 : 1;
   }
@@ -936,8 +1036,9 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.cluster = 2;
   const int unit = p.n_tiles * p.cluster;
   int grid = kNumSMs - (kNumSMs % unit);
-  const long long total = p.rows2 ? (long long)(p.m_tiles / 2) * unit
-                                  : (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
+  const long long total = p.rows4 ? (long long)(p.m_tiles / 4) * unit
+                          : p.rows2 ? (long long)(p.m_tiles / 2) * unit
+                                    : (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
   if (total < grid) grid = (int)total;
   if (stat_rows_out) *stat_rows_out = grid / p.n_tiles;
   if (dry) return 0;

@@ -23,6 +23,8 @@ SHAPES = [  # N, H, W, Cin, Cout
     (1, 4, 128, 128, 128),     # strip mode, N = 128
     (1, 8, 128, 16, 64),       # strip mode, stem (K chunk of 16)
     (2, 6, 256, 128, 64),      # strip mode, two-row work units (streamed weights, even height)
+    (2, 12, 256, 64, 64),      # strip mode, resident bank, four-row units with N-merged vertical taps
+    (1, 4, 128, 64, 64),       # the same, a single unit
     (1, 40, 64, 192, 64),      # wgrad strip ring wraps (mirror slot), two pieces per column
     (2, 40, 128, 64, 256),     # wgrad strip, 128-column variant + tap (2,2) on the split-K kernel
 ]
@@ -34,6 +36,29 @@ def _mk(N, H, W, Cin, Cout, seed=0):
     w = (torch.randn(Cout, 3, 3, Cin, device=DEV) * (1.0 / (3 * Cin ** 0.5))).to(torch.bfloat16)
     b = torch.randn(Cout, device=DEV)
     return x, w, b
+
+
+def test_fprop_four_row_units_forced(monkeypatch):
+    """The N-merged four-row units are the default for dgrad only; fprop takes them with B200SEG_ROWS4=2,
+    which has to be set before the library reads it, hence a subprocess."""
+    import subprocess
+    import sys
+    code = (
+        "import torch\n"
+        "from distributed_deep_learning_on_personal_computers_b200.ops import functional as Fn, reference as ref\n"
+        "torch.manual_seed(0)\n"
+        "for (N,H,W,Ci,Co) in ((2,12,256,64,64),(1,8,128,16,64)):\n"
+        "    x=torch.randn(N,H,W,Ci,device='cuda').bfloat16(); w=(torch.randn(Co,3,3,Ci,device='cuda')/(3*Ci**0.5)).bfloat16()\n"
+        "    b=torch.randn(Co,device='cuda'); y=torch.empty(N,H,W,Co,dtype=torch.bfloat16,device='cuda')\n"
+        "    part=Fn.conv3x3_fwd(x,w,b,y,want_stats=True,impl='tcgen05')\n"
+        "    yr,_=ref.conv3x3_fwd(x.float(),w.float(),b,want_stats=False)\n"
+        "    torch.testing.assert_close(y.float(),yr,rtol=2e-2,atol=2e-2)\n"
+        "    torch.testing.assert_close(part.sum(0)[0],y.float().sum((0,1,2)),rtol=1e-3,atol=1e-1)\n"
+        "print('ok')\n")
+    import os
+    env = dict(os.environ, B200SEG_ROWS4="2")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
 
 
 @pytest.mark.parametrize("shape", SHAPES)
