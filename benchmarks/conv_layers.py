@@ -67,7 +67,8 @@ def main():
         flops = 2.0 * N * H * W * 9 * cin * cout
         xn, wn, dyn = x.permute(0, 3, 1, 2), wt.permute(0, 3, 1, 2), dy.permute(0, 3, 1, 2)
         ops = {
-            "fprop": (lambda: Fn.conv3x3_fwd(x, wt, bias, y, True, impl="tcgen05"),
+            # no conv bias, as in the engine (BatchNorm absorbs it, see bn_finalize)
+            "fprop": (lambda: Fn.conv3x3_fwd(x, wt, None, y, True, impl="tcgen05"),
                       lambda: torch.nn.functional.conv2d(xn, wn, None, padding=1)),
             "dgrad": (lambda: Fn.conv3x3_dgrad(dy, wt, dx, impl="tcgen05"),
                       lambda: torch.nn.grad.conv2d_input(xn.shape, wn, dyn, padding=1)),

@@ -64,6 +64,7 @@ struct TapGemmParams {
   int cluster;                     // 1, or 2: CTA pairs (adjacent M tiles) share the weight tile via TMA multicast
   int rows2;                       // STRIP mode: a work unit is TWO vertically adjacent row tiles sharing every weight tile
   int rows4;                       // STRIP mode, resident bank, N = 64: FOUR-row units, vertical taps merged along N
+  int reg_stats;                   // N = 64: BN statistics accumulated in registers (B200SEG_REG_STATS=0 disables)
   int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
   int xslots;                      // STRIP mode: number of input-strip slots
   uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
@@ -100,7 +101,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   __shared__ __align__(8) uint64_t bar_xfull[kMaxXSlots], bar_xempty[kMaxXSlots];
   __shared__ __align__(8) uint64_t bar_tfull[4], bar_tempty[4];
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[256];
+  __shared__ __align__(16) float s_bias[256];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -498,9 +499,17 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 #pragma unroll
     for (int j = 0; j < 8; ++j) st_s[j] = st_q[j] = 0.f;
     const bool has_bias = p.bias != nullptr;
-    const bool want_stats = p.partials != nullptr;
     const bool ragged = ((p.W & (TW - 1)) | (p.H & (TH - 1))) != 0 || (p.N % p.tn) != 0;
     const int block_n = p.block_n;
+    // N = 64 (where this epilogue, not the MMAs, bounds the kernel): a thread always meets the same 32
+    // channels, so it keeps their sum / sum of squares in registers across ALL its tiles (2 instructions
+    // per element, on the fp32 accumulator values) instead of re-reading the staging tile (3 + a shared
+    // load); the rows are folded once, at the end of the kernel.
+    const bool reg_stats = p.partials != nullptr && p.reg_stats && block_n == 64 && !ragged && csz == 1;
+    const bool want_stats = p.partials != nullptr && !reg_stats;
+    float rs_s[32], rs_q[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) rs_s[j] = rs_q[j] = 0.f;
     int acc = 0;
     uint32_t acc_phase = 0;
     int sbuf = 0;
@@ -533,8 +542,16 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
         }
         tmem_ld_wait();
+        if (reg_stats) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float v = __uint_as_float(r[j]) + (has_bias ? s_bias[c0 + j] : 0.f);
+            rs_s[j] += v;
+            rs_q[j] = fmaf(v, v, rs_q[j]);
+          }
+        }
         // the 32 columns lie inside one group when ocb >= 32; for ocb == 16 they span two groups
-        uint8_t* const gbase = staging + (c0 >> ocb_log2) * group_bytes + my_row_off;
+        const uint32_t gbase = smem_u32(staging + (c0 >> ocb_log2) * group_bytes + my_row_off);
         const uint32_t ch0 = (c0 & (ocb - 1)) >> 3;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {                     // four 16-byte chunks of 8 channels
@@ -542,14 +559,22 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             float f[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
-            if (has_bias) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] += s_bias[c0 + v * 8 + j];
+            if (has_bias) {                               // two 16-byte shared loads per 8 channels
+              const float4 b0 = *reinterpret_cast<const float4*>(s_bias + c0 + v * 8);
+              const float4 b1 = *reinterpret_cast<const float4*>(s_bias + c0 + v * 8 + 4);
+              f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+              f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
             }
             uint32_t chunk = ch0 + v;
-            uint8_t* gb = gbase;
+            uint32_t gb = gbase;
             if (ocb == 16 && v >= 2) { chunk -= 2; gb += group_bytes; }
-            *reinterpret_cast<bf16x8*>(gb + ((chunk ^ my_rx) << 4)) = pack8(f);
+            // one st.shared.v4 (through a generic pointer the compiler emitted four 4-byte stores with
+            // 4-way bank conflicts: 37 % of the kernel's shared-memory wavefronts were excess)
+            const bf16x8 pk = pack8(f);
+            const uint32_t* pw = reinterpret_cast<const uint32_t*>(&pk);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(gb + ((chunk ^ my_rx) << 4)), "r"(pw[0]),
+                         "r"(pw[1]), "r"(pw[2]), "r"(pw[3])
+                         : "memory");
           }
         }
       }
@@ -620,7 +645,41 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       }
       named_bar_sync(1, kEpiThreads);
     }
-    if (p.partials != nullptr) {
+    if (reg_stats) {
+      // fold the 128 rows: butterfly inside each warp, then the four warps of a column half through smem
+      if (et == 0) tma_store_wait_read<0>();
+      named_bar_sync(1, kEpiThreads);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          rs_s[j] += __shfl_xor_sync(0xffffffffu, rs_s[j], o);
+          rs_q[j] += __shfl_xor_sync(0xffffffffu, rs_q[j], o);
+        }
+      }
+      float* red = reinterpret_cast<float*>(staging0);   // [8 warps][2][32]
+      if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          red[((warp - 2) * 2 + 0) * 32 + j] = rs_s[j];
+          red[((warp - 2) * 2 + 1) * 32 + j] = rs_q[j];
+        }
+      }
+      named_bar_sync(1, kEpiThreads);
+      if (et < 64) {                                      // channel et: column half et / 32, warps 4*half .. 4*half+3
+        const int half = et >> 5, j = et & 31;
+        float sv = 0.f, qv = 0.f;
+        for (int wq = 0; wq < 4; ++wq) {
+          sv += red[((half * 4 + wq) * 2 + 0) * 32 + j];
+          qv += red[((half * 4 + wq) * 2 + 1) * 32 + j];
+        }
+        const int col = n_tile * 64 + et;
+        if (col < p.n_total) {
+          p.partials[((size_t)prow * 2 + 0) * p.n_total + col] = sv;
+          p.partials[((size_t)prow * 2 + 1) * p.n_total + col] = qv;
+        }
+      }
+    } else if (p.partials != nullptr) {
       // combine the (128 / cpr) threads that share a chunk column, then one row of partials per CTA
       if (et == 0) tma_store_wait_read<0>();
       named_bar_sync(1, kEpiThreads);
@@ -964,6 +1023,11 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   if ((mode == 2 || mode == 3) && g.tn > 1 && (1 << g.th_log2) != H) return (int)cudaErrorInvalidValue;
   p.bias = bias;
   p.partials = partials;
+  {
+    static int rs_env = -1;
+    if (rs_env < 0) { const char* e = getenv("B200SEG_REG_STATS"); rs_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    p.reg_stats = rs_env;
+  }
   if (partials != nullptr && (p.block_n % 8 != 0 || p.block_n < 16 || p.block_n > 256)) return (int)cudaErrorInvalidValue;
   p.a_bytes = 128 * BK * 2;
   const bool bmn = (mode == 1 || mode == 3);

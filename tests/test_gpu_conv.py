@@ -53,7 +53,7 @@ def test_fprop_four_row_units_forced(monkeypatch):
         "    part=Fn.conv3x3_fwd(x,w,b,y,want_stats=True,impl='tcgen05')\n"
         "    yr,_=ref.conv3x3_fwd(x.float(),w.float(),b,want_stats=False)\n"
         "    torch.testing.assert_close(y.float(),yr,rtol=2e-2,atol=2e-2)\n"
-        "    torch.testing.assert_close(part.sum(0)[0],y.float().sum((0,1,2)),rtol=1e-3,atol=1e-1)\n"
+        "    torch.testing.assert_close(part.sum(0)[0],y.float().sum((0,1,2)),rtol=2e-3,atol=0.5)\n"
         "print('ok')\n")
     import os
     env = dict(os.environ, B200SEG_ROWS4="2")
@@ -72,8 +72,12 @@ def test_conv3x3_fprop_and_stats(shape):
     y_ref, _ = ref.conv3x3_fwd(x.float(), w.float(), b, want_stats=False)
     torch.testing.assert_close(y.float(), y_ref, rtol=2e-2, atol=2e-2)
     st = part.sum(0)
+    # the statistics are those of the conv output: of its bf16 rounding for wide tiles, of the fp32
+    # accumulators for 64-channel tiles (register path); both are within rounding noise of each other
     want = torch.stack([y.float().sum((0, 1, 2)), (y.float() ** 2).sum((0, 1, 2))])
-    torch.testing.assert_close(st, want, rtol=1e-3, atol=1e-1)
+    torch.testing.assert_close(st, want, rtol=2e-3, atol=0.5)
+    want32 = torch.stack([y_ref.sum((0, 1, 2)), (y_ref ** 2).sum((0, 1, 2))])
+    torch.testing.assert_close(st, want32, rtol=2e-3, atol=0.5)
 
 
 @pytest.mark.parametrize("shape", [s for s in SHAPES if s[3] != 16])
@@ -92,7 +96,7 @@ def test_conv3x3_dgrad(shape):
     part = Fn.conv3x3_dgrad_stats(dy, w, dx2, impl="tcgen05")
     assert torch.equal(dx2, dx.contiguous())
     want = torch.stack([dx2.float().sum((0, 1, 2)), (dx2.float() ** 2).sum((0, 1, 2))])
-    torch.testing.assert_close(part.sum(0), want, rtol=1e-3, atol=1e-1)
+    torch.testing.assert_close(part.sum(0), want, rtol=2e-3, atol=0.5)     # 64-column tiles sum the fp32 accumulators
 
 
 @pytest.mark.parametrize("shape", SHAPES)
