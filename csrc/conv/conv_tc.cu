@@ -79,6 +79,15 @@ struct KCfg {
   static constexpr uint32_t kSBO = 8 * kRowBytes;
 };
 
+// 16-byte shared-memory load through the shared window (a generic pointer makes the compiler emit four
+// 4-byte loads, which conflict 4-way on the swizzled staging tile)
+__device__ __forceinline__ bf16x8 lds128(uint32_t saddr) {
+  bf16x8 v;
+  uint32_t* w = reinterpret_cast<uint32_t*>(&v);
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(saddr));
+  return v;
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int n) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
 }
@@ -602,13 +611,13 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
       }
       if (want_stats && live) {
-        const uint8_t* gb = staging + st_grp * group_bytes;
+        const uint32_t gb = smem_u32(staging + st_grp * group_bytes);
         if (!ragged) {
 #pragma unroll 4
           for (int i = 0; i < st_rows; ++i) {
             const uint32_t ro = (st_rg + i * st_rstep) * row_bytes;
             float f[8];
-            unpack8(*reinterpret_cast<const bf16x8*>(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
+            unpack8(lds128(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
 #pragma unroll
             for (int j = 0; j < 8; ++j) { st_s[j] += f[j]; st_q[j] = fmaf(f[j], f[j], st_q[j]); }
           }
@@ -619,7 +628,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const bool valid = (w0 + tw_ < p.W) && (h0 + th_ < p.H) && (n0 + tn_ < p.N);
             const uint32_t ro = rr * row_bytes;
             float f[8];
-            unpack8(*reinterpret_cast<const bf16x8*>(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
+            unpack8(lds128(gb + ro + ((st_chunk ^ ((ro >> 7) & swz_mask)) << 4)), f);
             if (valid) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) { st_s[j] += f[j]; st_q[j] = fmaf(f[j], f[j], st_q[j]); }

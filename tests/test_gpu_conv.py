@@ -75,9 +75,10 @@ def test_conv3x3_fprop_and_stats(shape):
     # the statistics are those of the conv output: of its bf16 rounding for wide tiles, of the fp32
     # accumulators for 64-channel tiles (register path); both are within rounding noise of each other
     want = torch.stack([y.float().sum((0, 1, 2)), (y.float() ** 2).sum((0, 1, 2))])
-    torch.testing.assert_close(st, want, rtol=2e-3, atol=0.5)
+    noise = 0.02 * (N * H * W) ** 0.5
+    torch.testing.assert_close(st, want, rtol=2e-3, atol=noise)
     want32 = torch.stack([y_ref.sum((0, 1, 2)), (y_ref ** 2).sum((0, 1, 2))])
-    torch.testing.assert_close(st, want32, rtol=2e-3, atol=0.5)
+    torch.testing.assert_close(st, want32, rtol=2e-3, atol=noise)
 
 
 @pytest.mark.parametrize("shape", [s for s in SHAPES if s[3] != 16])
@@ -96,7 +97,9 @@ def test_conv3x3_dgrad(shape):
     part = Fn.conv3x3_dgrad_stats(dy, w, dx2, impl="tcgen05")
     assert torch.equal(dx2, dx.contiguous())
     want = torch.stack([dx2.float().sum((0, 1, 2)), (dx2.float() ** 2).sum((0, 1, 2))])
-    torch.testing.assert_close(part.sum(0), want, rtol=2e-3, atol=0.5)     # 64-column tiles sum the fp32 accumulators
+    # 64-column tiles sum the fp32 accumulators, wider ones the bf16-rounded tile: allow rounding noise
+    # (2^-9 per element, random sign) on top of the summation order
+    torch.testing.assert_close(part.sum(0), want, rtol=2e-3, atol=0.02 * (N * H * W) ** 0.5)
 
 
 @pytest.mark.parametrize("shape", SHAPES)
