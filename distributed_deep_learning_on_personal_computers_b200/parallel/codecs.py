@@ -80,7 +80,8 @@ class Codec:
         if self.wire_dtype == torch.bfloat16:
             return scale * 2.0 ** -8
         if self.wire_dtype == torch.float16:
-            return scale * 2.0 ** -11
+            # half an ulp of a normal number, or half the subnormal spacing (2^-24) below 2^-14
+            return max(scale * 2.0 ** -11, 2.0 ** -25)
         if _FP8 is not None and self.wire_dtype == _FP8:
             return scale * 2.0 ** -4
         return 0.0
