@@ -99,8 +99,9 @@ def _train_worker(rank, world, port, comm, q, out_dir):
                       LOCAL_RANK=str(rank))
     from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
     from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    comm, _, codec = comm.partition("-")               # "native-q201": the reference's 201-level wire format
     cfg = TrainConfig(base_channels=32, tile=64, train_tiles=32, holdout_tiles=0, batch_size=4, sync_every=2,
-                      epochs=2, codec="fp32", comm=comm, device="cuda", out_dir=out_dir, sample_images=0,
+                      epochs=2, codec=codec or "fp32", comm=comm, device="cuda", out_dir=out_dir, sample_images=0,
                       lr=2e-3, timeout_s=120).apply_env()
     tr = Trainer(cfg)
     losses = []
@@ -112,7 +113,7 @@ def _train_worker(rank, world, port, comm, q, out_dir):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("comm", ["native", "torch"])
+@pytest.mark.parametrize("comm", ["native", "torch", "native-q201"])
 def test_two_rank_training_replicas_identical(comm, tmp_path):
     world = 2
     ctx = mp.get_context("spawn")
@@ -126,7 +127,7 @@ def test_two_rank_training_replicas_identical(comm, tmp_path):
         p.join(timeout=60)
         assert p.exitcode == 0
     (_, b0, l0, d0), (_, b1, l1, d1) = res
-    assert b0 == b1 == comm
+    assert b0 == b1 == comm.split("-")[0]
     assert d0 == d1                                  # bit-identical replicas
     assert l0[-1] < l0[0]
 

@@ -77,3 +77,57 @@ def test_trainer_cuda_graph_loss_decreases(tmp_path):
     p = tr.save(str(tmp_path / "c.pt"))
     tr2 = Trainer(TrainConfig(**{**cfg.to_dict(), "resume": p, "out_dir": str(tmp_path / "b")}))
     torch.testing.assert_close(tr2.model.flat["param"], tr.model.flat["param"])
+
+
+def test_engine_bilinear_mode_matches_oracle():
+    """The bilinear up-sampling variant (R:609) through the GPU engine against the CPU oracles."""
+    torch.manual_seed(1)
+    own = UNet(out_classes=6, up_sample_mode="bilinear", base_channels=32).cuda()
+    cpu = UNet(out_classes=6, up_sample_mode="bilinear", base_channels=32)
+    cpu.load_state_dict(own.state_dict())
+    own.flatten_parameters(torch.device("cuda"))
+    cpu.flatten_parameters(torch.device("cpu"))
+    N, H, W = 4, 128, 128                                  # as above: fewer images make the 4x4-level BNs too noisy
+    img = torch.randint(0, 256, (N, H, W, 3), dtype=torch.uint8, device="cuda")
+    lab = torch.randint(0, 6, (N, H, W), dtype=torch.uint8, device="cuda")
+    eng = NativeEngine(own, N, H, W)
+    eng.load_batch(img, lab)
+    out = eng.train_microbatch().clone()
+    eng_cpu = NativeEngine(cpu, N, H, W, act_dtype=torch.bfloat16)
+    eng_cpu.load_batch(img.cpu(), lab.cpu())
+    out_cpu = eng_cpu.train_microbatch().clone()
+    assert abs(out[0].item() - out_cpu[0].item()) / out_cpu[0].item() < 2e-2
+    table = []
+    for (n, p), (_, q) in zip(own.named_parameters(), cpu.named_parameters()):
+        if n.endswith((".0.bias", ".3.bias")) and "double_conv" in n:
+            continue
+        cos = torch.nn.functional.cosine_similarity(p.grad.float().flatten().cpu(), q.grad.float().flatten(), dim=0).item()
+        table.append((cos, n))
+    import os
+    os.makedirs("gpurun_out", exist_ok=True)
+    open("gpurun_out/grad_cosines_bilinear.txt", "w").write("\n".join(f"{c:.4f} {n}" for c, n in table) + "\n")
+    # bf16 rounding noise grows faster with depth here than with the transposed conv (smooth up-sampled
+    # features, small gradient signal at random init); the CPU oracle with the same rounding points shows
+    # the same distance to fp32 autograd layer by layer (0.71 at the stem for both), so only the direction
+    # is checked away from the loss
+    for cos, n in table:
+        floor = 0.99 if n.startswith("conv_last") else (0.95 if n.startswith("up_conv1.double_conv") else 0.75)
+        assert cos > floor, (n, cos)
+
+
+@pytest.mark.parametrize("optimizer", ["adam", "sgd"])
+def test_trainer_accumulates_k_microbatches_under_graph(tmp_path, optimizer):
+    """The reference's loop shape: K micro-batches accumulate, then one exchange + step (R:756-759)."""
+    cfg = TrainConfig(base_channels=32, tile=64, train_tiles=24, holdout_tiles=0, batch_size=2, sync_every=3,
+                      epochs=3, world_size=1, codec="fp32", device="cuda", out_dir=str(tmp_path), sample_images=0,
+                      optimizer=optimizer, lr=2e-3 if optimizer == "adam" else 5e-2, momentum=0.9)
+    tr = Trainer(cfg)
+    losses = []
+    for _ in range(4):
+        st = tr.train_epoch()
+        losses.append(st["mean_loss"])
+        tr.epoch += 1
+    assert st["micro_batches"] == 12
+    assert tr.optimizer.step_count == 16                       # 4 epochs x 12 micro-batches / 3
+    assert losses[-1] < losses[0]
+    assert float(tr.model.flat["grad"].abs().max()) == 0.0     # zeroed by the fused step
