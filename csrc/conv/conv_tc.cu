@@ -748,6 +748,10 @@ struct WgradParams {
   int quads;                                // convT: output quadrants per CTA (4 = all share one x tile), else 1
 };
 
+// CSZ = 2: CTA pairs (two adjacent M tiles of the same N tile and K slice) share every dy tile: each CTA
+// fetches half of its 64-channel blocks and TMA-multicasts them into both, which takes a quarter to a
+// third off the L2 traffic of a kernel that is L2-bound on the deep layers (64 B/clk/SM demanded).
+template <int CSZ>
 __global__ void __launch_bounds__(kConvThreads, 1)
 wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
              const WgradParams p) {
@@ -759,9 +763,16 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   int id = blockIdx.x;
-  const int n_tile = id % p.n_tiles; id /= p.n_tiles;
-  const int m_tile = id % p.m_tiles; id /= p.m_tiles;
+  int n_tile, m_tile;
+  if (CSZ == 2) {                        // the two CTAs of a cluster are adjacent M tiles
+    m_tile = id % p.m_tiles; id /= p.m_tiles;
+    n_tile = id % p.n_tiles; id /= p.n_tiles;
+  } else {
+    n_tile = id % p.n_tiles; id /= p.n_tiles;
+    m_tile = id % p.m_tiles; id /= p.m_tiles;
+  }
   const int ks = id;
+  const int crank = (CSZ == 2) ? (int)cluster_ctarank() : 0;
   const int per = (p.p_tiles + p.k_slices - 1) / p.k_slices;
   const int pt0 = ks * per;
   const int pt1 = min(p.p_tiles, pt0 + per);
@@ -770,13 +781,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_dy);
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], CSZ); }
     mbar_init(&bar_tfull, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
   tc_fence_before();
   __syncthreads();
+  if (CSZ == 2) cluster_sync_all();      // the peer's barriers exist before anything is multicast
   tc_fence_after();
   pdl_wait();                 // everything above overlapped the previous kernel's tail (see common.cuh)
   pdl_trigger();
@@ -805,15 +817,26 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0);
           }
           if (!p.convt) {
-            for (int nb = 0; nb < nblocks; ++nb)
-              tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
+            for (int nb = 0; nb < nblocks; ++nb) {
+              if (CSZ == 1)
+                tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
+              else if ((nb & 1) == crank)
+                tma_load_4d_mc(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0,
+                               (uint16_t)3);
+            }
           } else {
             for (int qi = 0; qi < p.quads; ++qi) {
               const int q = p.quads == 4 ? qi : n_tile / p.nt_per_q;
               const int nt = p.quads == 4 ? n_tile : n_tile % p.nt_per_q;
-              for (int nb = 0; nb < nblocks; ++nb)
-                tma_load_5d(sb + (qi * nblocks + nb) * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64,
-                            q & 1, w0, q >> 1, n0 * p.H + h0);
+              for (int nb = 0; nb < nblocks; ++nb) {
+                const int bi = qi * nblocks + nb;
+                if (CSZ == 1)
+                  tma_load_5d(sb + bi * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0, q >> 1,
+                              n0 * p.H + h0);
+                else if ((bi & 1) == crank)
+                  tma_load_5d_mc(sb + bi * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0,
+                                 q >> 1, n0 * p.H + h0, (uint16_t)3);
+              }
             }
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -847,7 +870,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
                           (it | k4) != 0 ? 1u : 0u);
             }
           }
-          umma_commit(&bar_empty[stage]);
+          if (CSZ == 1) umma_commit(&bar_empty[stage]);
+          else umma_commit_mc(&bar_empty[stage], (uint16_t)3);     // frees the stage in both CTAs of the pair
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
         umma_commit(&bar_tfull);
@@ -909,6 +933,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  if (CSZ == 2) cluster_sync_all();      // no CTA leaves while its peer may still multicast into it
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
@@ -1287,13 +1312,34 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   }
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(kSmemBudget + 2048));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSmemBudget + 2048));
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
   const size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
-  return (int)launch_k(wgrad_kernel, base_items * ks, kConvThreads, smem, st, mx, mdy, p);
+  // CTA pairs sharing the dy tile: needs an even number of M tiles (the pair) and of dy blocks (the halves)
+  static int wcl_env = -1;
+  if (wcl_env < 0) { const char* e = getenv("B200SEG_WGRAD_CLUSTER"); wcl_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  const int nbt = p.quads * nblocks;
+  if (wcl_env && p.m_tiles % 2 == 0 && nbt % 2 == 0) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(base_items * ks);
+    cfg.blockDim = dim3(kConvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, wgrad_kernel<2>, mx, mdy, p);
+  }
+  return (int)launch_k(wgrad_kernel<1>, base_items * ks, kConvThreads, smem, st, mx, mdy, p);
 }
 
 extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout);
