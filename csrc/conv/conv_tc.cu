@@ -751,6 +751,10 @@ struct WgradParams {
 // CSZ = 2: CTA pairs (two adjacent M tiles of the same N tile and K slice) share every dy tile: each CTA
 // fetches half of its 64-channel blocks and TMA-multicasts them into both, which takes a quarter to a
 // third off the L2 traffic of a kernel that is L2-bound on the deep layers (64 B/clk/SM demanded).
+// CSZ = 4: a 2 x 2 cluster (two M tiles x two N tiles); the x tile is shared along N the same way, so
+// every CTA fetches half of each operand (32 B/clk/SM, below what L2 delivers).  A stage may be
+// refilled once the consumers of every CTA that is written into have released it: the MMA thread's
+// commit goes to itself and to the two peers it shares an operand with.
 template <int CSZ>
 __global__ void __launch_bounds__(kConvThreads, 1)
 wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
@@ -764,7 +768,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
 
   int id = blockIdx.x;
   int n_tile, m_tile;
-  if (CSZ == 2) {                        // the two CTAs of a cluster are adjacent M tiles
+  const int crank = (CSZ > 1) ? (int)cluster_ctarank() : 0;
+  const int m_bit = crank & 1, n_bit = crank >> 1;
+  if (CSZ == 4) {                        // cluster = (M pair) x (N pair)
+    id >>= 2;
+    const int mp = p.m_tiles >> 1, np = p.n_tiles >> 1;
+    m_tile = 2 * (id % mp) + m_bit; id /= mp;
+    n_tile = 2 * (id % np) + n_bit; id /= np;
+  } else if (CSZ == 2) {                 // the two CTAs of a cluster are adjacent M tiles
     m_tile = id % p.m_tiles; id /= p.m_tiles;
     n_tile = id % p.n_tiles; id /= p.n_tiles;
   } else {
@@ -772,7 +783,10 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
     m_tile = id % p.m_tiles; id /= p.m_tiles;
   }
   const int ks = id;
-  const int crank = (CSZ == 2) ? (int)cluster_ctarank() : 0;
+  const uint16_t mask_b = (uint16_t)(3u << (2 * n_bit));                 // the M pair of this N tile
+  const uint16_t mask_a = (uint16_t)((1u << m_bit) | (1u << (m_bit + 2)));   // the N pair of this M tile
+  const uint16_t mask_c = (CSZ == 4) ? (uint16_t)((1u << crank) | (1u << (crank ^ 1)) | (1u << (crank ^ 2)))
+                                     : (uint16_t)3;
   const int per = (p.p_tiles + p.k_slices - 1) / p.k_slices;
   const int pt0 = ks * per;
   const int pt1 = min(p.p_tiles, pt0 + per);
@@ -781,14 +795,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_dy);
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], CSZ); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], CSZ == 4 ? 3 : CSZ); }
     mbar_init(&bar_tfull, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_base_s);
   tc_fence_before();
   __syncthreads();
-  if (CSZ == 2) cluster_sync_all();      // the peer's barriers exist before anything is multicast
+  if (CSZ > 1) cluster_sync_all();       // the peers' barriers exist before anything is multicast
   tc_fence_after();
   pdl_wait();                 // everything above overlapped the previous kernel's tail (see common.cuh)
   pdl_trigger();
@@ -814,15 +828,18 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             if (blk >= p.m_blocks) blk = p.m_blocks - 1;     // padding block: loaded, never stored
             const int t = p.tap0 + blk / p.chunks_per_tap, cc = blk % p.chunks_per_tap;
             const int dw_ = p.convt ? 0 : (t % 3 - 1), dh_ = p.convt ? 0 : (t / 3 - 1);
-            tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0);
+            if (CSZ < 4)
+              tma_load_4d(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0);
+            else if ((hb & 1) == n_bit)
+              tma_load_4d_mc(sa + hb * 8192, &map_x, &bar_full[stage], cc * 64, w0 + dw_, h0 + dh_, n0, mask_a);
           }
           if (!p.convt) {
             for (int nb = 0; nb < nblocks; ++nb) {
               if (CSZ == 1)
                 tma_load_4d(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0);
-              else if ((nb & 1) == crank)
+              else if ((nb & 1) == m_bit)
                 tma_load_4d_mc(sb + nb * 8192, &map_dy, &bar_full[stage], n_tile * p.block_n + nb * 64, w0, h0, n0,
-                               (uint16_t)3);
+                               mask_b);
             }
           } else {
             for (int qi = 0; qi < p.quads; ++qi) {
@@ -833,9 +850,9 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
                 if (CSZ == 1)
                   tma_load_5d(sb + bi * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0, q >> 1,
                               n0 * p.H + h0);
-                else if ((bi & 1) == crank)
+                else if ((bi & 1) == m_bit)
                   tma_load_5d_mc(sb + bi * 8192, &map_dy, &bar_full[stage], nt * p.block_n + nb * 64, q & 1, w0,
-                                 q >> 1, n0 * p.H + h0, (uint16_t)3);
+                                 q >> 1, n0 * p.H + h0, mask_b);
               }
             }
           }
@@ -871,7 +888,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             }
           }
           if (CSZ == 1) umma_commit(&bar_empty[stage]);
-          else umma_commit_mc(&bar_empty[stage], (uint16_t)3);     // frees the stage in both CTAs of the pair
+          else umma_commit_mc(&bar_empty[stage], mask_c);          // frees the stage in every CTA written into
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
         umma_commit(&bar_tfull);
@@ -933,7 +950,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (CSZ == 2) cluster_sync_all();      // no CTA leaves while its peer may still multicast into it
+  if (CSZ > 1) cluster_sync_all();       // no CTA leaves while a peer may still multicast into it
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
@@ -1316,15 +1333,21 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
                                          (int)(kSmemBudget + 2048));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSmemBudget + 2048));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(wgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSmemBudget + 2048));
     if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
   const size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
   // CTA pairs sharing the dy tile: needs an even number of M tiles (the pair) and of dy blocks (the halves)
+  // B200SEG_WGRAD_CLUSTER: 0 none, 2 pairs (default), 4 also 2 x 2 clusters where the tiling allows.  The
+  // 2 x 2 form is correct but measured slower (L3.c1 0.387 vs 0.259 ms, L3.dec0 0.699 vs 0.471): four CTAs
+  // in lock step over a 3-stage ring lose more than the halved x traffic gains.
   static int wcl_env = -1;
-  if (wcl_env < 0) { const char* e = getenv("B200SEG_WGRAD_CLUSTER"); wcl_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  if (wcl_env < 0) { const char* e = getenv("B200SEG_WGRAD_CLUSTER"); wcl_env = (e == nullptr) ? 2 : (e[0] == '0' ? 0 : (e[0] == '4' ? 4 : 2)); }
   const int nbt = p.quads * nblocks;
   if (wcl_env && p.m_tiles % 2 == 0 && nbt % 2 == 0) {
+    const bool quad = wcl_env == 4 && p.quads == 1 && p.n_tiles % 2 == 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(base_items * ks);
     cfg.blockDim = dim3(kConvThreads);
@@ -1332,11 +1355,12 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.x = quad ? 4 : 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    if (quad) return (int)cudaLaunchKernelEx(&cfg, wgrad_kernel<4>, mx, mdy, p);
     return (int)cudaLaunchKernelEx(&cfg, wgrad_kernel<2>, mx, mdy, p);
   }
   return (int)launch_k(wgrad_kernel<1>, base_items * ks, kConvThreads, smem, st, mx, mdy, p);
