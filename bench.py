@@ -25,7 +25,6 @@ import os
 import subprocess
 import sys
 import threading
-import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -252,7 +251,6 @@ def run_reference(args, dctx, torch):
         model = reference_unet(args.base_channels, 6).cuda()
     except Exception as exc:
         return {"impl": "reference", "unavailable": f"{type(exc).__name__}: {exc}"[:200]}
-    import torch.nn.functional as F
     from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
     world, rank, local = dctx["world"], dctx["rank"], dctx["local"]
     torch.backends.cudnn.benchmark = True

@@ -4,7 +4,6 @@
     python benchmarks/profile_step.py --impl own|reference [--conv tcgen05|cudnn] [--out FILE]
 """
 import argparse
-import json
 import os
 import sys
 

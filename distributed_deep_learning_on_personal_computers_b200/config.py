@@ -13,7 +13,7 @@ import argparse
 import dataclasses
 import json
 import os
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Optional
 
 CODECS = ("fp32", "bf16", "fp16", "q201", "q21", "int8s", "fp8")

@@ -19,7 +19,7 @@ plain-PyTorch oracle (``ops.reference``) on CPU, so this file is testable agains
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
 import torch

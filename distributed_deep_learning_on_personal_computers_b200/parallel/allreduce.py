@@ -29,7 +29,7 @@ Reduction semantics: ``mean`` is the exact mean over ``world_size`` 
 from __future__ import annotations
 
 import time
-from typing import Dict, List, Optional
+from typing import Dict
 
 import torch
 import torch.distributed as dist

@@ -20,7 +20,6 @@ from __future__ import annotations
 import datetime
 import os
 from dataclasses import dataclass
-from typing import Optional
 
 import torch
 import torch.distributed as dist

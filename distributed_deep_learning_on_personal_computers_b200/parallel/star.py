@@ -28,7 +28,7 @@ import struct
 import time
 import zlib
 from concurrent.futures import ThreadPoolExecutor
-from typing import Any, Dict, List, Optional, Sequence
+from typing import Any, Dict, List, Optional
 
 import msgpack
 import numpy as np

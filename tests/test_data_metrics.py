@@ -1,10 +1,9 @@
 import os
 
-import numpy as np
 import torch
 
 from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
-from distributed_deep_learning_on_personal_computers_b200.utils import data, metrics, checkpoint
+from distributed_deep_learning_on_personal_computers_b200.utils import data, metrics
 from distributed_deep_learning_on_personal_computers_b200.config import parse_cli
 
 
