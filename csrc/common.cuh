@@ -96,14 +96,20 @@ __device__ __forceinline__ void quad_transpose32(uint32_t (&v)[32], int lane) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-inline bool pdl_enabled() {
+// B200SEG_PDL: 0 off (default), 1 every kernel that supports it, 2 only the small elementwise kernels
+// (level 1 = tensor-core kernels too).
+inline int pdl_level() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("B200SEG_PDL"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
-  return v == 1;
+  if (v < 0) { const char* e = getenv("B200SEG_PDL"); v = (e == nullptr) ? 0 : (e[0] == '1' ? 1 : (e[0] == '2' ? 2 : 0)); }
+  return v;
 }
+#ifndef B200SEG_PDL_CLASS
+#define B200SEG_PDL_CLASS 1        // translation units of elementwise kernels define 2 before including this
+#endif
+static inline bool pdl_enabled() { return pdl_level() == 1 || (pdl_level() == 2 && B200SEG_PDL_CLASS == 2); }
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                             Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;

@@ -8,6 +8,7 @@
 //   concat buffer, which removes torch.cat, R:616) and, for encoder blocks, the pooled tensor.
 // Backward is reduce -> finalize -> apply; the pool's arg-max is recomputed from y (first
 // maximum in row-major window order, as ATen), so no index tensor is stored.
+#define B200SEG_PDL_CLASS 2
 #include "../common.cuh"
 #include "b200seg.h"
 

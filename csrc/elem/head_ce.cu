@@ -9,6 +9,7 @@
 //     dl = (softmax(z) - onehot(y_p)) * grad_scale;   da_p = W^T dl;   dW += dl a_p^T;  db += dl
 // Reductions (dW, db, loss, correct) are deterministic: per-CTA partials in a workspace, summed
 // in CTA order by the last CTA to finish.
+#define B200SEG_PDL_CLASS 2
 #include "../common.cuh"
 #include "b200seg.h"
 #include <cstdio>
