@@ -13,11 +13,15 @@ struct __align__(16) bf16x8 {
   __nv_bfloat162 v[4];
 };
 
+// 16-byte accesses, spelled as uint4: copying the struct member by member made the compiler emit four
+// 4-byte LDG / STG per access in every kernel that used these (found in the SASS; 4x the memory
+// instructions and partial-sector stores).
 __device__ __forceinline__ bf16x8 ld8(const __nv_bfloat16* p) {
-  return *reinterpret_cast<const bf16x8*>(p);
+  const uint4 t = *reinterpret_cast<const uint4*>(p);
+  return *reinterpret_cast<const bf16x8*>(&t);
 }
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const bf16x8& x) {
-  *reinterpret_cast<bf16x8*>(p) = x;
+  *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&x);
 }
 __device__ __forceinline__ void unpack8(const bf16x8& x, float (&f)[8]) {
 #pragma unroll
