@@ -267,9 +267,11 @@ __device__ __forceinline__ void load_g(const __nv_bfloat16* __restrict__ d_out, 
     for (int j = 0; j < 8; ++j) g[k][j] = (a[k][j] > 0.f) ? g[k][j] : 0.f;
 }
 
+// Register caps chosen by measurement (profiles/variants_in_situ.txt): the pooled variants keep a 2x2
+// window of three tensors live and run best at 2 CTAs / SM; the plain reduce is fastest with the compiler's own choice
+// (119 registers, 8 loads in flight per thread; any explicit cap measured 25-45 % slower), the plain apply at 3 CTAs / SM (78 registers, no spills).
 template <bool POOL>
-__global__ void __launch_bounds__(kThreads)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
+__device__ __forceinline__ void bn_bwd_reduce_body(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
                      const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
                      const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
                      int N, int H, int W, int C, float* __restrict__ partial) {
@@ -343,6 +345,25 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
   }
 }
 
+template <bool POOL>
+__global__ void bn_bwd_reduce_kernel(const __nv_bfloat16* d_out, long long ld_do, const __nv_bfloat16* d_pool,
+                                     long long ld_dp, const __nv_bfloat16* y, long long ld_y, const float* ss, int N,
+                                     int H, int W, int C, float* partial);
+template <>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel<false>(const __nv_bfloat16* d_out, long long ld_do, const __nv_bfloat16* d_pool, long long ld_dp,
+                            const __nv_bfloat16* y, long long ld_y, const float* ss, int N, int H, int W, int C,
+                            float* partial) {
+  bn_bwd_reduce_body<false>(d_out, ld_do, d_pool, ld_dp, y, ld_y, ss, N, H, W, C, partial);
+}
+template <>
+__global__ void __launch_bounds__(kThreads, 2)
+bn_bwd_reduce_kernel<true>(const __nv_bfloat16* d_out, long long ld_do, const __nv_bfloat16* d_pool, long long ld_dp,
+                           const __nv_bfloat16* y, long long ld_y, const float* ss, int N, int H, int W, int C,
+                           float* partial) {
+  bn_bwd_reduce_body<true>(d_out, ld_do, d_pool, ld_dp, y, ld_y, ss, N, H, W, C, partial);
+}
+
 // Backward pass 2 (tiny): finish the two sums, accumulate dgamma / dbeta, and fold everything the
 // apply pass needs into 3 per-channel coefficients: dy = k1*g + e1*y + e0.
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int rows, long long count,
@@ -374,7 +395,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int ro
 }
 
 template <bool POOL>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, POOL ? 2 : 3)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ d_out, long long ld_do,
                     const __nv_bfloat16* __restrict__ d_pool, long long ld_dp,
                     const __nv_bfloat16* __restrict__ y, long long ld_y, const float* __restrict__ ss,
