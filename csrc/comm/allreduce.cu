@@ -71,7 +71,8 @@ template <> struct Wire<float> {
 template <> struct Wire<__nv_bfloat16> {
   static constexpr int kVec = 8;
   __device__ static void load(const void* p, size_t i, float (&f)[8]) {
-    unpack8(reinterpret_cast<const bf16x8*>(p)[i], f);
+    const uint4 v = reinterpret_cast<const uint4*>(p)[i];      // one 16-byte load (a bf16x8 copy became four)
+    unpack8(*reinterpret_cast<const bf16x8*>(&v), f);
   }
 };
 template <> struct Wire<__half> {
