@@ -30,6 +30,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BASELINE_TILES_PER_S = None      # BASELINE.md publishes no throughput number -> vs_baseline null
+# BASELINE.json configs (config 5, the all-reduce sweep, is benchmarks/allreduce_sweep.py)
+PRESETS = {
+    "headline": {"base_channels": 64, "tile": 512, "batch": 16},
+    "b128": {"base_channels": 128, "tile": 512, "batch": 16},
+    "tile1024": {"base_channels": 64, "tile": 1024, "batch": 2},
+    "shipped": {"base_channels": 32, "tile": 512, "batch": 1},
+}
 
 
 def parse():
@@ -46,7 +53,14 @@ def parse():
     p.add_argument("--conv", default=None, help="tcgen05 | cudnn (own arm only)")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
-    return p.parse_args()
+    p.add_argument("--no-overlap", action="store_true", help="exchange after backward (whole buffer) instead of under it")
+    p.add_argument("--preset", default=None, choices=sorted(PRESETS),
+                   help="BASELINE.json configs: headline (2, default), b128 (3), tile1024 (4), shipped (reference as shipped)")
+    a = p.parse_args()
+    if a.preset:
+        for k, v in PRESETS[a.preset].items():
+            setattr(a, k, v)
+    return a
 
 
 class ClockSampler:
@@ -195,7 +209,8 @@ def run_own(args, dctx, torch):
                       sync_every=1, codec=args.codec, comm=args.comm, world_size=world, rank=rank,
                       local_rank=local, train_tiles=n_tiles, holdout_tiles=0, sample_images=0,
                       cuda_graph=not args.no_graph, out_dir=os.path.join(ROOT, "gpurun_out", "bench_run"),
-                      shard_data=False, shuffle=False, device="cuda")
+                      shard_data=False, shuffle=False, device="cuda", overlap=not args.no_overlap,
+                      check_peers_every=0)
     ctx = pdist.DistContext(rank, world, local, torch.device("cuda", local),
                             "nccl" if world > 1 else "none", False)
     tiles = synthetic_tiles(n_tiles, args.tile, 6, seed=rank)
@@ -205,9 +220,7 @@ def run_own(args, dctx, torch):
 
     def step_resident(i):
         img, lab = dev_batches[i % 3]
-        tr.micro_step(img, lab)
-        tr.pending = 1
-        tr.sync_and_step()
+        tr.train_step(img, lab)       # forward + loss + backward (gradient buckets reduced under it) + Adam
 
     for i in range(max(args.warmup, 3)):
         step_resident(i)
@@ -227,18 +240,22 @@ def run_own(args, dctx, torch):
 
         def step_e2e(i):
             img, lab = next(it)                      # H2D from pinned memory on the copy stream
-            out = tr.micro_step(img, lab)
-            tr.pending = 1
-            tr.sync_and_step()
+            out = tr.train_step(img, lab)
             host_loss.copy_(out, non_blocking=False)  # D2H read of the step's loss / accuracy
 
         for i in range(max(args.warmup, 3)):
             step_e2e(i)
         ms_e2e = timed(step_e2e, args.steps, dctx, torch)
         h2d, d2h = tr.loader.bytes_per_batch, 8
+    tr.check_peers()
     extra = {"engine": "native", "conv": os.environ.get("B200SEG_CONV", "tcgen05"),
              "comm": ("fused" if tr.sync.fused else tr.sync.backend), "codec": args.codec, "cuda_graph": not args.no_graph,
-             "allreduce": (tr.sync.native.algorithm if tr.sync.native is not None else None)}
+             "allreduce": (None if tr.sync.native is None else
+                           (("nvls" if tr.overlap.multicast_ptr else "twoshot") + "-bucketed-under-backward"
+                            if tr.overlap is not None else tr.sync.native.algorithm)),
+             "grad_buckets": (len(tr.overlap.ovl_buckets) if tr.overlap is not None else 0),
+             # every B200SEG_* switch in effect (they select kernel variants; recorded so no run is ambiguous)
+             "env": {k: v for k, v in sorted(os.environ.items()) if k.startswith("B200SEG_")}}
     return _result(args, dctx, "own", ms, ms_e2e, clk, launches, h2d, d2h, extra)
 
 

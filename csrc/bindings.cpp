@@ -289,6 +289,35 @@ void write_mult(const Tensor& scale, double levels, Tensor out) {
   ok(b200seg_write_mult(f32(scale), (float)levels, f32(out), cur()), "write_mult");
 }
 
+void arm_next_wgrad(int64_t arm_ptr) { b200seg_arm_next_wgrad(reinterpret_cast<const void*>(arm_ptr)); }
+
+void bucket_reduce(int64_t multicast_ptr, at::IntArrayRef grad_ptrs, at::IntArrayRef pad_ptrs, Tensor state,
+                   int64_t rank, int64_t bucket, bool self_publish, bool final_bucket, at::IntArrayRef offs,
+                   at::IntArrayRef counts, double post_scale, double timeout_s, int64_t blocks) {
+  const int world = (int)pad_ptrs.size();
+  TORCH_CHECK(world >= 2 && world <= 16 && (grad_ptrs.empty() || (int)grad_ptrs.size() == world),
+              "bucket_reduce: bad pointer lists");
+  TORCH_CHECK(state.is_cuda() && state.scalar_type() == at::kInt && state.numel() >= 2 && state.is_contiguous(),
+              "bucket_reduce: state must be a CUDA int32[2]");
+  TORCH_CHECK(offs.size() == counts.size() && offs.size() >= 1 && offs.size() <= 4, "bucket_reduce: 1..4 ranges");
+  c10::cuda::CUDAGuard g(state.device());
+  float* gp[16]; unsigned int* pp[16];
+  for (int r = 0; r < world; ++r) {
+    gp[r] = grad_ptrs.empty() ? nullptr : reinterpret_cast<float*>(grad_ptrs[r]);
+    pp[r] = reinterpret_cast<unsigned int*>(pad_ptrs[r]);
+  }
+  long long o[4], c[4];
+  for (size_t i = 0; i < offs.size(); ++i) { o[i] = offs[i]; c[i] = counts[i]; }
+  ok(b200seg_bucket_reduce(reinterpret_cast<float*>(multicast_ptr), grad_ptrs.empty() ? nullptr : gp, pp,
+                           reinterpret_cast<unsigned int*>(state.data_ptr<int>()), (int)rank, world, (int)bucket,
+                           self_publish ? 1 : 0, final_bucket ? 1 : 0, (int)offs.size(), o, c, (float)post_scale,
+                           timeout_s, (int)blocks, cur()), "bucket_reduce");
+}
+int64_t overlap_pad_words() { return b200seg_overlap_pad_words(); }
+int64_t overlap_max_buckets() { return b200seg_overlap_max_buckets(); }
+int64_t overlap_flag_index(int64_t bucket, int64_t rank) { return b200seg_overlap_flag_index((int)bucket, (int)rank); }
+int64_t overlap_abort_index() { return b200seg_overlap_abort_index(); }
+
 int64_t allreduce_signal_bytes() { return b200seg_allreduce_signal_bytes(); }
 int64_t allreduce_max_blocks() { return b200seg_allreduce_max_blocks(); }
 
@@ -343,6 +372,14 @@ TORCH_LIBRARY(b200seg, m) {
         "int blocks) -> ()", &allreduce_nvls);
   m.def("peer_barrier(int[] signal_ptrs, int rank, int epoch) -> ()", &peer_barrier);
   m.def("set_grad_multicast(Tensor buf, int n_elems, int multicast_ptr) -> ()", &set_grad_multicast);
+  m.def("arm_next_wgrad(int arm_ptr) -> ()", &arm_next_wgrad);
+  m.def("bucket_reduce(int multicast_ptr, int[] grad_ptrs, int[] pad_ptrs, Tensor(a!) state, int rank, int bucket, "
+        "bool self_publish, bool final_bucket, int[] offs, int[] counts, float post_scale, float timeout_s, "
+        "int blocks) -> ()", &bucket_reduce);
+  m.def("overlap_pad_words() -> int", &overlap_pad_words);
+  m.def("overlap_max_buckets() -> int", &overlap_max_buckets);
+  m.def("overlap_flag_index(int bucket, int rank) -> int", &overlap_flag_index);
+  m.def("overlap_abort_index() -> int", &overlap_abort_index);
   m.def("allreduce_signal_bytes() -> int", &allreduce_signal_bytes);
   m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);

@@ -93,6 +93,39 @@ __device__ __forceinline__ void quad_transpose32(uint32_t (&v)[32], int lane) {
   }
 }
 
+// ---- all-reduce trigger carried by a weight-gradient kernel (csrc/comm/overlap.cu) ------------------
+// A `GradArm` lives in device memory (built by parallel/symm.py, one per gradient bucket).  The wgrad
+// launch that completes a bucket gets a pointer to it; every CTA calls grad_arm_publish() after its last
+// red.global.add, the LAST one to arrive tells every rank -- this one included -- that the bucket is ready
+// by storing the current exchange number into flags[bucket][this rank] of each rank's signal pad.  These
+// are peer stores over NVLink issued from the same kernel that ran the UMMA tiles.
+constexpr int kArmMaxRanks = 16;
+struct GradArm {
+  unsigned int* counter;                    // local; wraps back to 0 when the last CTA arrives
+  const unsigned int* epoch;                // local; exchange number, advanced by the final bucket's reduce kernel
+  unsigned int* peer_flag[kArmMaxRanks];    // flags[bucket][this rank] in every rank's pad
+  int world;
+  int pad_;
+};
+// Must be reached by ALL threads of the CTA (it contains a __syncthreads).
+__device__ __forceinline__ void grad_arm_publish(const GradArm* arm) {
+  if (arm == nullptr) return;
+  __threadfence();                                         // this thread's reductions are performed at L2
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int total = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned int old = atomicInc(arm->counter, total - 1);
+    if (old == total - 1) {                                // every CTA of the launch has arrived
+      __threadfence();
+      const unsigned int e = *reinterpret_cast<const volatile unsigned int*>(arm->epoch);
+      __threadfence_system();
+      for (int r = 0; r < arm->world; ++r)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(arm->peer_flag[r]), "r"(e) : "memory");
+    }
+  }
+}
+extern "C" const void* b200seg_take_grad_arm();           // one-shot arm set by b200seg_arm_next_wgrad
+
 // Programmatic dependent launch (B200SEG_PDL=1): a kernel may be scheduled while its predecessor in the
 // stream drains; pdl_wait() blocks until the predecessor has completed and its writes are visible, so
 // everything before it (barrier init, TMEM allocation, descriptor prefetch, CTA ramp-up) overlaps the

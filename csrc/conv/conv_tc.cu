@@ -288,13 +288,39 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer ========================================
-    if (STRIP && elect_one()) {
+    // ONE elected lane runs the loops (ptxas then knows the stream is single-threaded and keeps barrier
+    // addresses, descriptors and counters in uniform registers; a lane-0 predicate inside a warp-wide
+    // loop made it wrap every UMMA in an ELECT / R2UR.BROADCAST waterfall instead).  All shared-window
+    // addresses are computed once, here.
+    if (elect_one()) {
+    constexpr bool issuer = true;
+    const uint32_t a_full = hold(smem_u32(bar_full)), a_empty = hold(smem_u32(bar_empty));
+    const uint32_t a_xfull = hold(smem_u32(bar_xfull)), a_xempty = hold(smem_u32(bar_xempty));
+    const uint32_t a_tfull = hold(smem_u32(bar_tfull)), a_tempty = hold(smem_u32(bar_tempty));
+    const uint32_t a_ring = hold(smem_u32(smem)), a_xring = hold(smem_u32(xring));
+    const uint32_t stage_bytes = hold(p.stage_bytes), xslot_bytes = hold(p.xslot_bytes);
+    const int n_stages = (int)hold((uint32_t)p.stages), n_xslots = (int)hold((uint32_t)p.xslots);
+    const int kc_per_tap = (int)hold((uint32_t)p.kc_per_tap);
+    const bool resident = hold((uint32_t)p.b_resident) != 0;
+    const uint32_t tmem_b = hold(tmem_base);
+    constexpr uint32_t kRowB = KCfg<BLOCK_K>::kRowBytes;
+    constexpr uint32_t A_HI = desc_hi(KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+    constexpr uint32_t B_HI = B_MN ? desc_hi(1024, LAYOUT_SW128) : A_HI;
+    constexpr uint32_t B_LBO = B_MN ? BLOCK_K * 128 : 16;
+    constexpr uint32_t A_K4 = 32 >> 4, B_K4 = B_MN ? (2048 >> 4) : (32 >> 4);
+    constexpr int K4N = BLOCK_K / 16;
+    auto release_a = [&](uint32_t bar_addr) {
+      if (csz == 1) umma_commit_a(bar_addr); else umma_commit_mc_a(bar_addr, cmask);
+    };
+    if (STRIP) {
       const uint32_t idesc = make_idesc_bf16(128, p.block_n, 0, B_MN ? 1 : 0);
       int stage = 0, xs = 0;
       uint32_t phase = 0, xphase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      if (p.b_resident) MBAR_WAIT_OR_TRAP(&bar_full[0], 0);
+      const uint32_t win0 = (p.flip > 0) ? 0u : 2u * kRowB;              // operand window of sft = 0 ...
+      const uint32_t win_step = (p.flip > 0) ? kRowB : (0u - kRowB);     // ... and the step to the next tap
+      if (resident) mbar_wait_a(a_full, 0);
       if (p.rows4) {
         // Four output rows per unit, 64 columns each, side by side in one 256-column accumulator.  Input
         // strip j (image row h0-1+j) feeds output rows j-2 .. j through the three filter rows; because the
@@ -305,176 +331,169 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         const uint32_t idesc_n[4] = {0u, make_idesc_bf16(128, 64, 0, B_MN ? 1 : 0), make_idesc_bf16(128, 128, 0, B_MN ? 1 : 0),
                                      make_idesc_bf16(128, 192, 0, B_MN ? 1 : 0)};
         for (int q = m_first; q < (p.m_tiles >> 2); q += m_step) {
-          MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+          mbar_wait_a(a_tempty + 8 * acc, acc_phase ^ 1);
           tc_fence_after();
-          const uint32_t d0 = tmem_base + acc * 256;
+          const uint32_t d0 = tmem_b + acc * 256;
 #pragma unroll
           for (int j = 0; j < 6; ++j) {
-            MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
+            mbar_wait_a(a_xfull + 8 * xs, xphase);
             tc_fence_after();
-            const uint64_t da_strip = make_smem_desc(smem_u32(xring + (size_t)xs * p.xslot_bytes), 16,
-                                                     KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+            const uint32_t sx = a_xring + xs * xslot_bytes;
             const int sub_min = j > 2 ? j - 2 : 0, sub_max = j < 3 ? j : 3;
             const int nb = sub_max - sub_min + 1;
             const int first_blk = j < 2 ? 2 - j : 0;
             const bool has_new = j <= 3;                   // output row j gets its first contribution here
+            if (issuer) {
 #pragma unroll
-            for (int sft = 0; sft < 3; ++sft) {
-              const int win = (p.flip > 0) ? sft : 2 - sft;
-              const uint64_t da0 = da_strip + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
-              const uint32_t sb = smem_u32(smem + (size_t)(sft * 3 + first_blk) * p.stage_bytes);
-              const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
-                                        : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
-              if (sft == 0 && has_new) {
-                const int nb_old = nb - 1;
-                if (nb_old > 0) {
+              for (int sft = 0; sft < 3; ++sft) {
+                const uint32_t a_lo = desc_lo(sx + win0 + sft * win_step, 16);
+                const uint32_t b_lo = desc_lo(a_ring + (sft * 3 + first_blk) * stage_bytes, B_LBO);
+                if (sft == 0 && has_new) {
+                  const int nb_old = nb - 1;
+                  if (nb_old > 0) {
 #pragma unroll
-                  for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
-                    umma_bf16(d0 + sub_min * 64, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
-                              idesc_n[nb_old], 1u);
+                    for (int k4 = 0; k4 < K4N; ++k4)
+                      umma_bf16_lh(d0 + sub_min * 64, a_lo + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc_n[nb_old], 1u);
+                  }
+                  const uint32_t bn_lo = b_lo + ((nb_old * stage_bytes) >> 4);
+#pragma unroll
+                  for (int k4 = 0; k4 < K4N; ++k4)
+                    umma_bf16_lh(d0 + j * 64, a_lo + k4 * A_K4, A_HI, bn_lo + k4 * B_K4, B_HI, idesc_n[1], k4 == 0 ? 0u : 1u);
+                } else {
+#pragma unroll
+                  for (int k4 = 0; k4 < K4N; ++k4)
+                    umma_bf16_lh(d0 + sub_min * 64, a_lo + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc_n[nb], 1u);
                 }
-                const uint64_t dbn = db0 + ((nb_old * p.stage_bytes) >> 4);
-#pragma unroll
-                for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
-                  umma_bf16(d0 + j * 64, da0 + ((k4 * 32) >> 4), dbn + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
-                            idesc_n[1], k4 == 0 ? 0u : 1u);
-              } else {
-#pragma unroll
-                for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
-                  umma_bf16(d0 + sub_min * 64, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4),
-                            idesc_n[nb], 1u);
               }
+              umma_commit_a(a_xempty + 8 * xs);
             }
-            umma_commit(&bar_xempty[xs]);
-            if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+              if (++xs == n_xslots) { xs = 0; xphase ^= 1; }
           }
-          umma_commit(&bar_tfull[acc]);
+          if (issuer) umma_commit_a(a_tfull + 8 * acc);
           if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
       } else if (p.rows2) {
         for (int q = m_first; q < (p.m_tiles >> 1); q += m_step) {
           // accumulator slots acc, acc+1 (of 4, 128 columns each) hold output rows h0 and h0+1
-          MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
-          MBAR_WAIT_OR_TRAP(&bar_tempty[acc + 1], acc_phase ^ 1);
+          mbar_wait_a(a_tempty + 8 * acc, acc_phase ^ 1);
+          mbar_wait_a(a_tempty + 8 * (acc + 1), acc_phase ^ 1);
           tc_fence_after();
-          const uint32_t d0 = tmem_base + acc * 128, d1 = d0 + 128;
-          uint32_t first = 0;
-          for (int kc = 0; kc < p.kc_per_tap; ++kc) {
-            uint64_t dstrip[4];
-            int xslot[4];
+          const uint32_t d0 = tmem_b + acc * 128, d1 = d0 + 128;
+          for (int kc = 0; kc < kc_per_tap; ++kc) {
+            uint32_t sxs[4];
+            int xs0 = xs;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
-              xslot[j] = xs;
-              dstrip[j] = make_smem_desc(smem_u32(xring + (size_t)xs * p.xslot_bytes), 16, KCfg<BLOCK_K>::kSBO,
-                                         KCfg<BLOCK_K>::kLayout);
-              if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+              mbar_wait_a(a_xfull + 8 * xs, xphase);
+              sxs[j] = a_xring + xs * xslot_bytes;
+              if (++xs == n_xslots) { xs = 0; xphase ^= 1; }
             }
             tc_fence_after();
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
               const int r = t / 3, sft = t % 3;
-              MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+              mbar_wait_a(a_full + 8 * stage, phase);
               tc_fence_after();
-              const int win = (p.flip > 0) ? sft : 2 - sft;
               // input strip of output row `sub` for filter row r: sub + r (fprop) or sub + 2 - r (dgrad)
-              const int j0 = (p.flip > 0) ? r : 2 - r;
-              const uint64_t a0 = dstrip[j0] + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
-              const uint64_t a1 = dstrip[j0 + 1] + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
-              const uint32_t sb = smem_u32(smem + (size_t)stage * p.stage_bytes);
-              const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
-                                        : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+              const uint32_t woff = win0 + sft * win_step;
+              const uint32_t s0 = (p.flip > 0) ? sxs[r] : sxs[2 - r];
+              const uint32_t s1 = (p.flip > 0) ? sxs[r + 1] : sxs[3 - r];
+              const uint32_t a0 = desc_lo(s0 + woff, 16), a1 = desc_lo(s1 + woff, 16);
+              const uint32_t b_lo = desc_lo(a_ring + stage * stage_bytes, B_LBO);
+              const uint32_t accf = (kc | t) != 0 ? 1u : 0u;
+              if (issuer) {
 #pragma unroll
-              for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
-                const uint64_t bk = db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4);
-                umma_bf16(d0, a0 + ((k4 * 32) >> 4), bk, idesc, first);
-                umma_bf16(d1, a1 + ((k4 * 32) >> 4), bk, idesc, first);
-                first = 1u;
+                for (int k4 = 0; k4 < K4N; ++k4) {
+                  umma_bf16_lh(d0, a0 + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc, k4 == 0 ? accf : 1u);
+                  umma_bf16_lh(d1, a1 + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc, k4 == 0 ? accf : 1u);
+                }
+                release_a(a_empty + 8 * stage);
               }
-              release_b(&bar_empty[stage]);
-              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                  if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
+            if (issuer) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) umma_commit(&bar_xempty[xslot[j]]);
+              for (int j = 0; j < 4; ++j) umma_commit_a(a_xempty + 8 * (xs0 + j));   // four slots never straddle the ring end
+            }
+            }
+          if (issuer) {
+            umma_commit_a(a_tfull + 8 * acc);
+            umma_commit_a(a_tfull + 8 * (acc + 1));
           }
-          umma_commit(&bar_tfull[acc]);
-          umma_commit(&bar_tfull[acc + 1]);
           acc += 2;
           if (acc == 4) { acc = 0; acc_phase ^= 1; }
         }
-      } else
-      for (int mu = m_first; mu < m_units; mu += m_step) {
-        const int m = min(mu * csz + crank, p.m_tiles - 1);
-        MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * 256;
-        uint32_t first = 0;
-        for (int kr = 0; kr < p.kc_per_tap * 3; ++kr) {
-          MBAR_WAIT_OR_TRAP(&bar_xfull[xs], xphase);
+      } else {
+        const int kr_n = kc_per_tap * 3;
+        const uint32_t tap_pitch = kc_per_tap * stage_bytes;          // resident bank: distance between taps
+        for (int mu = m_first; mu < m_units; mu += m_step) {
+          mbar_wait_a(a_tempty + 8 * acc, acc_phase ^ 1);
           tc_fence_after();
-          const uint32_t sx = smem_u32(xring + (size_t)xs * p.xslot_bytes);
-          const uint64_t da_strip = make_smem_desc(sx, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
-          const int kc_ = kr / 3, r_ = kr - kc_ * 3;
+          const uint32_t d_tmem = tmem_b + acc * 256;
+          int kc_ = 0, r_ = 0;
+          for (int kr = 0; kr < kr_n; ++kr) {
+            mbar_wait_a(a_xfull + 8 * xs, xphase);
+            tc_fence_after();
+            const uint32_t sx = a_xring + xs * xslot_bytes;
+            const uint32_t bank0 = a_ring + (r_ * 3 * kc_per_tap + kc_) * stage_bytes;
 #pragma unroll
-          for (int sft = 0; sft < 3; ++sft) {
-            if (!p.b_resident) {
-              MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
-              tc_fence_after();
-            }
-            // window of 128 pixel rows starting (1 + flip*(sft-1)) rows into the strip
-            const int win = (p.flip > 0) ? sft : 2 - sft;
-            const uint64_t da0 = da_strip + ((win * KCfg<BLOCK_K>::kRowBytes) >> 4);
-            const int slot = p.b_resident ? ((r_ * 3 + sft) * p.kc_per_tap + kc_) : stage;
-            const uint32_t sb = smem_u32(smem + (size_t)slot * p.stage_bytes);
-            const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
-                                      : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+            for (int sft = 0; sft < 3; ++sft) {
+              uint32_t sb = bank0 + sft * tap_pitch;
+              if (!resident) {
+                mbar_wait_a(a_full + 8 * stage, phase);
+                tc_fence_after();
+                sb = a_ring + stage * stage_bytes;
+              }
+              // window of 128 pixel rows starting (1 + flip*(sft-1)) rows into the strip
+              const uint32_t a_lo = desc_lo(sx + win0 + sft * win_step, 16);
+              const uint32_t b_lo = desc_lo(sb, B_LBO);
+              const uint32_t accf = (kr | sft) != 0 ? 1u : 0u;
+              if (issuer) {
 #pragma unroll
-            for (int k4 = 0; k4 < BLOCK_K / 16; ++k4) {
-              umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc, first);
-              first = 1u;
+                for (int k4 = 0; k4 < K4N; ++k4)
+                  umma_bf16_lh(d_tmem, a_lo + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc, k4 == 0 ? accf : 1u);
+                if (!resident) release_a(a_empty + 8 * stage);
+              }
+                  if (!resident) { if (++stage == n_stages) { stage = 0; phase ^= 1; } }
             }
-            if (!p.b_resident) {
-              release_b(&bar_empty[stage]);
-              if (++stage == p.stages) { stage = 0; phase ^= 1; }
-            }
+            if (issuer) umma_commit_a(a_xempty + 8 * xs);     // all three taps of this strip are issued
+              if (++xs == n_xslots) { xs = 0; xphase ^= 1; }
+            if (++r_ == 3) { r_ = 0; ++kc_; }
           }
-          umma_commit(&bar_xempty[xs]);                    // all three taps of this strip are issued
-          if (++xs == p.xslots) { xs = 0; xphase ^= 1; }
+          if (issuer) umma_commit_a(a_tfull + 8 * acc);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        umma_commit(&bar_tfull[acc]);
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
-    } else if (!STRIP && elect_one()) {
+    } else {
       const uint32_t idesc = make_idesc_bf16(128, p.block_n, 0, B_MN ? 1 : 0);
+      const uint32_t a_bytes = p.a_bytes;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int mu = m_first; mu < m_units; mu += m_step) {
-        const int m = min(mu * csz + crank, p.m_tiles - 1);
-        MBAR_WAIT_OR_TRAP(&bar_tempty[acc], acc_phase ^ 1);
+        mbar_wait_a(a_tempty + 8 * acc, acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * 256;
+        const uint32_t d_tmem = tmem_b + acc * 256;
         for (int it = 0; it < k_iters; ++it) {
-          MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
+          mbar_wait_a(a_full + 8 * stage, phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
-          const uint32_t sb = sa + p.a_bytes;
-          // descriptors: build once per stage, then only bump the 14-bit address field per K step
-          const uint64_t da0 = make_smem_desc(sa, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
-          const uint64_t db0 = B_MN ? make_smem_desc(sb, BLOCK_K * 128, 1024, LAYOUT_SW128)
-                                    : make_smem_desc(sb, 16, KCfg<BLOCK_K>::kSBO, KCfg<BLOCK_K>::kLayout);
+          const uint32_t sa = a_ring + stage * stage_bytes;
+          const uint32_t a_lo = desc_lo(sa, 16), b_lo = desc_lo(sa + a_bytes, B_LBO);
+          const uint32_t accf = it != 0 ? 1u : 0u;
+          if (issuer) {
 #pragma unroll
-          for (int k4 = 0; k4 < BLOCK_K / 16; ++k4)
-            umma_bf16(d_tmem, da0 + ((k4 * 32) >> 4), db0 + ((B_MN ? k4 * 2048 : k4 * 32) >> 4), idesc,
-                      (it | k4) != 0 ? 1u : 0u);
-          release_b(&bar_empty[stage]);                   // frees the smem stage (in both CTAs of a pair)
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            for (int k4 = 0; k4 < K4N; ++k4)
+              umma_bf16_lh(d_tmem, a_lo + k4 * A_K4, A_HI, b_lo + k4 * B_K4, B_HI, idesc, k4 == 0 ? accf : 1u);
+            release_a(a_empty + 8 * stage);                 // frees the smem stage (in both CTAs of a pair)
+          }
+          if (++stage == n_stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&bar_tfull[acc]);                     // accumulator complete
+        if (issuer) umma_commit_a(a_tfull + 8 * acc);       // accumulator complete
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
+    }   // elect_one
   } else {
     // ===================================== epilogue ==========================================
     // The epilogue is instruction-issue bound for the narrow (N = 64) layers, so everything that does
@@ -746,6 +765,7 @@ struct WgradParams {
   int tap0;                                 // first filter tap handled (m_blocks counts taps from here)
   long long mc_delta;                       // != 0: add through the multicast alias (fused all-reduce)
   int quads;                                // convT: output quadrants per CTA (4 = all share one x tile), else 1
+  const GradArm* arm;                       // != NULL: this launch completes a gradient bucket (all-reduce trigger)
 };
 
 // CSZ = 2: CTA pairs (two adjacent M tiles of the same N tile and K slice) share every dy tile: each CTA
@@ -860,39 +880,52 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
         }
       }
     } else if (warp == 1) {
+      // single elected lane, addresses computed once (see tap_gemm_kernel)
       if (elect_one()) {
-        const uint32_t idesc = make_idesc_bf16(128, p.block_n, 1, 1);
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int it = 0; it < k_iters; ++it) {
-          MBAR_WAIT_OR_TRAP(&bar_full[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
-          const uint64_t db0 = make_smem_desc(sa + p.a_bytes, 8192, 1024, LAYOUT_SW128);
-          if (p.quads == 4) {                               // convT: the four quadrants share the x tile
-            const uint64_t da0 = make_smem_desc(sa, 8192, 1024, LAYOUT_SW128);
+      constexpr bool issuer = true;
+      const uint32_t a_full = hold(smem_u32(bar_full)), a_empty = hold(smem_u32(bar_empty));
+      const uint32_t a_tfull = hold(smem_u32(&bar_tfull));
+      const uint32_t a_ring = hold(smem_u32(smem));
+      const uint32_t stage_bytes = hold(p.stage_bytes), a_bytes = hold(p.a_bytes);
+      const int n_stages = (int)hold((uint32_t)p.stages), mt_n = (int)hold((uint32_t)p.mt);
+      const uint32_t tmem_b = hold(tmem_base);
+      const bool quads4 = p.quads == 4;
+      const uint32_t idesc = make_idesc_bf16(128, p.block_n, 1, 1);
+      constexpr uint32_t HI = desc_hi(1024, LAYOUT_SW128);
+      const uint32_t q_step = (uint32_t)(nblocks * 8192) >> 4;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < k_iters; ++it) {
+        mbar_wait_a(a_full + 8 * stage, phase);
+        tc_fence_after();
+        const uint32_t sa = a_ring + stage * stage_bytes;
+        const uint32_t b_lo = desc_lo(sa + a_bytes, 8192);
+        const uint32_t accf = it != 0 ? 1u : 0u;
+        if (issuer) {
+          if (quads4) {                                     // convT: the four quadrants share the x tile
+            const uint32_t a_lo = desc_lo(sa, 8192);
+#pragma unroll
             for (int qi = 0; qi < 4; ++qi) {
-              const uint64_t dbq = db0 + ((qi * nblocks * 8192) >> 4);
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4)
-                umma_bf16(tmem_base + qi * 128, da0 + ((k4 * 2048) >> 4), dbq + ((k4 * 2048) >> 4), idesc,
-                          (it | k4) != 0 ? 1u : 0u);
+                umma_bf16_lh(tmem_b + qi * 128, a_lo + k4 * 128, HI, b_lo + qi * q_step + k4 * 128, HI, idesc,
+                             k4 == 0 ? accf : 1u);
             }
           } else {
-            for (int t = 0; t < p.mt; ++t) {                // the M tiles of this CTA share the dy tile
-              const uint64_t da0 = make_smem_desc(sa + t * 16384, 8192, 1024, LAYOUT_SW128);
+            for (int t = 0; t < mt_n; ++t) {                // the M tiles of this CTA share the dy tile
+              const uint32_t a_lo = desc_lo(sa + t * 16384, 8192);
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4)
-                umma_bf16(tmem_base + t * 256, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
-                          (it | k4) != 0 ? 1u : 0u);
+                umma_bf16_lh(tmem_b + t * 256, a_lo + k4 * 128, HI, b_lo + k4 * 128, HI, idesc, k4 == 0 ? accf : 1u);
             }
           }
-          if (CSZ == 1) umma_commit(&bar_empty[stage]);
-          else umma_commit_mc(&bar_empty[stage], mask_c);          // frees the stage in every CTA written into
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          if (CSZ == 1) umma_commit_a(a_empty + 8 * stage);
+          else umma_commit_mc_a(a_empty + 8 * stage, mask_c);      // frees the stage in every CTA written into
         }
-        umma_commit(&bar_tfull);
+        if (++stage == n_stages) { stage = 0; phase ^= 1; }
       }
+      if (issuer) umma_commit_a(a_tfull);
+      }   // elect_one
     } else {
       const int rb = warp & 3;
       const int row = rb * 32 + lane;
@@ -948,6 +981,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
       }
     }
   }
+  grad_arm_publish(p.arm);               // all-reduce trigger: the last CTA tells every rank the bucket is ready
   tc_fence_before();
   __syncthreads();
   if (CSZ > 1) cluster_sync_all();       // no CTA leaves while a peer may still multicast into it
@@ -1310,6 +1344,7 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   p.k_slices = ks;
   p.dw = dw;
   p.mc_delta = b200seg_grad_multicast_delta(dw);
+  p.arm = static_cast<const GradArm*>(b200seg_take_grad_arm());   // this is always the last launch of a wgrad call
   CUtensorMap mx, mdy;
   const int TW = 1 << g.tw_log2, TH = 1 << g.th_log2;
   {

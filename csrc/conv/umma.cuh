@@ -63,8 +63,87 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity,
 }
 #define MBAR_WAIT_OR_TRAP(bar, parity)                      \
   do {                                                      \
-    if (!b200::mbar_wait((bar), (parity))) { asm volatile("trap;"); } \
+    if (!b200::mbar_wait((bar), (parity))) b200::mbar_timeout_trap(b200::smem_u32(bar), (parity)); \
   } while (0)
+
+// ---- lean forms for the MMA-issuing warp --------------------------------------------------------
+// The warp that feeds the tensor core is a single instruction stream; ncu (profiles/ncu_mma_issue.txt)
+// showed it, not the tensor pipe, bounding the 64-channel layers: ~140 instructions per 12 UMMAs, most of
+// them generic->shared conversions (S2UR SR_CgaCtaId), R2UR moves out of a divergent branch and
+// parameter re-loads.  These variants take 32-bit shared-window addresses computed ONCE, and the
+// issuing loops run warp-uniformly (every lane walks the loop, lane 0 issues), so descriptor
+// arithmetic stays in uniform registers.
+// Pins a value in a register: the compiler otherwise RE-DERIVES shared-window addresses (S2UR SR_CgaCtaId +
+// ULEA, a long-latency special-register read) and kernel parameters (LDC) at every use inside the loop.
+__device__ __forceinline__ uint32_t hold(uint32_t x) {
+  asm volatile("mov.b32 %0, %0;" : "+r"(x));
+  return x;
+}
+__device__ __forceinline__ bool mbar_try_a(uint32_t addr, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, P;\n\t}"
+      : "=r"(ok)
+      : "r"(addr), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait on a barrier given by address; a protocol error traps (it must not hang the box) after
+// recording which barrier it was in the error record: `g_error_record` points at pinned HOST memory
+// (mapped, set once per translation unit through b200seg_set_error_record), so the record survives the
+// dead context and the host can say which wait timed out (ops/loader.py last_device_error()).
+static __device__ unsigned int* g_error_record = nullptr;
+static __device__ __noinline__ void mbar_timeout_trap(uint32_t addr, uint32_t parity) {
+  unsigned int* rec = g_error_record;
+  if (rec != nullptr) {
+    rec[1] = addr;
+    rec[2] = parity;
+    rec[3] = blockIdx.x;
+    rec[4] = threadIdx.x;
+    __threadfence_system();
+    rec[0] = 0xB200DEADu;
+    __threadfence_system();
+  }
+  asm volatile("trap;");
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {
+#pragma unroll 1
+  for (uint32_t i = 0; i < 200000000u; ++i)
+    if (mbar_try_a(addr, parity)) return;
+  mbar_timeout_trap(addr, parity);
+}
+__device__ __forceinline__ void umma_commit_a(uint32_t bar_addr) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_addr)
+               : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc_a(uint32_t bar_addr, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          bar_addr),
+      "h"(mask)
+      : "memory");
+}
+// Descriptors as (lo, hi) 32-bit halves: hi (stride / version / layout) is loop-invariant and lo is the
+// 14-bit address field plus the leading-offset field, so stepping an operand is ONE 32-bit add.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes, uint32_t layout_type) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | ((layout_type & 7u) << 29);
+}
+__device__ __forceinline__ void umma_bf16_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                             uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 
 // ---- TMA ------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {

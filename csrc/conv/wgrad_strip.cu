@@ -53,6 +53,7 @@ struct WgradStripParams {
   int wsegs, rows_per_piece, pieces_per_col, pieces;   // pieces per group
   float* dw;
   long long mc_delta;                  // != 0: add through the multicast alias (fused all-reduce)
+  const GradArm* arm;                  // != NULL: this launch completes a gradient bucket (all-reduce trigger)
 };
 
 // Work distribution ("stream-K" over pixels): the (group, piece) pairs -- group = (Cin chunk, Cout tile),
@@ -143,55 +144,67 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     }
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer ----------------------------------
-    if (elect_one() && has_work) {
+    // One elected lane; shared-window addresses computed once (see tap_gemm_kernel).
+    if (has_work && elect_one()) {
+      constexpr bool issuer = true;
       const uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
-      const uint32_t sbase = smem_u32(smem);
+      const uint32_t sbase = hold(smem_u32(smem));
+      const uint32_t a_full = hold(smem_u32(bar_full)), a_empty = hold(smem_u32(bar_empty));
+      const uint32_t a_done = hold(smem_u32(&bar_done)), a_drained = hold(smem_u32(&bar_drained));
+      const uint32_t tmem_b = hold(tmem_base);
+      constexpr uint32_t HI = desc_hi(1024, LAYOUT_SW128);
       uint32_t q = 0;
-      bool first = true;
+      // ring positions of the strips holding filter rows 0, 1, 2 of the current step
+      uint32_t st0 = kWsStages - 2, st1 = kWsStages - 1, st2 = 0, ph2 = 0;
+      uint32_t first_step = 0;                              // 0: the next step overwrites the accumulators
       int cur_group = g0 / p.pieces;
       uint32_t seg_no = 0;
       for (int gid = g0; gid < g1;) {
         const WsSpan sp = ws_span(p, gid, g1);
         gid = sp.next;
         if (sp.group != cur_group) {                        // group boundary: hand the accumulators over
-          umma_commit(&bar_done);
-          MBAR_WAIT_OR_TRAP(&bar_drained, seg_no & 1);      // ... and wait until they have been read out
+          if (issuer) umma_commit_a(a_done);
+          mbar_wait_a(a_drained, seg_no & 1);               // ... and wait until they have been read out
           tc_fence_after();
           ++seg_no;
           cur_group = sp.group;
-          first = true;
+          first_step = 0;
         }
         const int nst = (sp.h1 - sp.h0) + 2;
         for (int j = 0; j < nst; ++j, ++q) {
-          const int st = q % kWsStages;
-          MBAR_WAIT_OR_TRAP(&bar_full[st], (q / kWsStages) & 1);
-          if (j < 2) continue;                              // halo rows of the span: loaded only
-          tc_fence_after();
-          const uint32_t strip0 = sbase + ((q - 2) % kWsStages) * kWsStageBytes;   // filter row 0
-          const uint32_t strip1 = sbase + ((q - 1) % kWsStages) * kWsStageBytes;
-          const uint32_t strip2 = sbase + st * kWsStageBytes;
-          const uint64_t db0 = make_smem_desc(strip2 + kStripBytes, 8192, 1024, LAYOUT_SW128);
-          const uint32_t acc0 = first ? 0u : 1u;
+          mbar_wait_a(a_full + 8 * st2, ph2);
+          if (j >= 2) {                                     // j < 2: halo rows of the span, loaded only
+            tc_fence_after();
+            const uint32_t strip0 = sbase + st0 * kWsStageBytes;   // filter row 0
+            const uint32_t strip1 = sbase + st1 * kWsStageBytes;
+            const uint32_t strip2 = sbase + st2 * kWsStageBytes;
+            const uint32_t b_lo = desc_lo(strip2 + kStripBytes, 8192);
+            const uint32_t a_t[5] = {desc_lo(strip0, 128), desc_lo(strip1, 128), desc_lo(strip2, 128),
+                                     desc_lo(strip0 + 256, kWsStageBytes),      // + mirror slot across the wrap
+                                     desc_lo(strip2 + 256, 128)};
+            if (issuer) {
+              // k-step outer, accumulator inner: consecutive UMMAs never hit the same accumulator (a chain
+              // of dependent N = 64 instructions is latency-bound, not throughput-bound)
 #pragma unroll
-          for (int t = 0; t < kTiles; ++t) {
-            uint64_t da0;
-            if (t < 3) da0 = make_smem_desc(t == 0 ? strip0 : (t == 1 ? strip1 : strip2), 128, 1024, LAYOUT_SW128);
-            else if (t == 3) da0 = make_smem_desc(strip0 + 256, kWsStageBytes, 1024, LAYOUT_SW128);   // + mirror
-            else da0 = make_smem_desc(strip2 + 256, 128, 1024, LAYOUT_SW128);
+              for (int k4 = 0; k4 < 4; ++k4) {
 #pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4)
-              umma_bf16(tmem_base + t * BN, da0 + ((k4 * 2048) >> 4), db0 + ((k4 * 2048) >> 4), idesc,
-                        k4 == 0 ? acc0 : 1u);
+                for (int t = 0; t < kTiles; ++t)
+                  umma_bf16_lh(tmem_b + t * BN, a_t[t] + k4 * 128, HI, b_lo + k4 * 128, HI, idesc,
+                               k4 == 0 ? first_step : 1u);
+              }
+              umma_commit_a(a_empty + 8 * st0);             // oldest strip is no longer needed
+              if (j == nst - 1) {                           // end of the span: free the other two
+                umma_commit_a(a_empty + 8 * st1);
+                umma_commit_a(a_empty + 8 * st2);
+              }
+            }
+              first_step = 1u;
           }
-          first = false;
-          umma_commit(&bar_empty[(q - 2) % kWsStages]);    // oldest strip is no longer needed
-          if (j == nst - 1) {                               // end of the span: free the other two
-            umma_commit(&bar_empty[(q - 1) % kWsStages]);
-            umma_commit(&bar_empty[st]);
-          }
+          st0 = st1; st1 = st2;
+          if (++st2 == kWsStages) { st2 = 0; ph2 ^= 1; }
         }
       }
-      umma_commit(&bar_done);
+      if (issuer) umma_commit_a(a_done);
     }
   } else if (has_work) {
     // ------------------------------------------------ epilogue (once per group touched) -----------
@@ -243,6 +256,7 @@ wgrad_strip_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       mbar_arrive(&bar_drained);                            // the MMA thread may overwrite the accumulators
     }
   }
+  grad_arm_publish(p.arm);               // all-reduce trigger (csrc/common.cuh)
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<512>(tmem_base);
@@ -326,7 +340,12 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
     int box[4] = {64, 64, 1, 1};
     if (!make_map(&mdy, dy, 4, dims, str, box, 128)) return (int)cudaErrorInvalidValue;
   }
-  if (bn == 64) return launch_strip<64>(mx, mdy, p, grid, st);
+  // the bucket trigger belongs to the LAST launch of this call: here, or the tap-(2,2) split-K launch below
+  p.arm = nullptr;
+  if (bn == 64) {
+    p.arm = static_cast<const GradArm*>(b200seg_take_grad_arm());
+    return launch_strip<64>(mx, mdy, p, grid, st);
+  }
   int rc = launch_strip<128>(mx, mdy, p, grid, st);
   if (rc != 0) return rc;
   return b200conv_wgrad_taps(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, 8, 1, st);   // tap (2,2)

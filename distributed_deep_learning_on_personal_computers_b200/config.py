@@ -57,7 +57,8 @@ class TrainConfig:
     compress_threads: int = 12       # mgzip thread count (R:43)
     compress_block: int = 1_000_000  # mgzip blocksize (R:51)
     comm: str = "auto"               # auto | native | fused | torch | star
-    bucket_mb: float = 25.0
+    overlap: bool = True             # native transport: reduce gradient buckets UNDER backward (R:756-763 does it after)
+    bucket_mb: float = 8.0           # bucket size of the overlapped exchange (whole U-Net blocks are never split)
     # ---- runtime ---------------------------------------------------------------------------
     device: str = "auto"             # auto | cuda | cpu
     dtype: str = "auto"              # auto | bf16 | fp32
@@ -71,7 +72,8 @@ class TrainConfig:
     world_size: int = 2              # N_conn + 1 with N_conn = 1 (R:223)
     rank: int = 0
     local_rank: int = 0
-    timeout_s: float = 600.0         # the reference blocks forever
+    timeout_s: float = 600.0         # the reference blocks forever; also bounds device-side waits
+    check_peers_every: int = 200     # optimizer steps between host checks of the device-side abort word (0: epoch end only)
     # ---- outputs (R:715-716, R:781-790) ----------------------------------------------------
     out_dir: str = "runs/default"
     log_name: Optional[str] = None   # default otus_{codec}.txt, as in R:715

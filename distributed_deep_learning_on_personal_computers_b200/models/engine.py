@@ -81,6 +81,11 @@ class NativeEngine:
         if self.stem_pad:
             self.stem_w = torch.zeros(cout, 3, 3, IN_PAD, dtype=self.act_dtype, device=self.device)
             self.stem_dw = torch.zeros(cout, 3, 3, IN_PAD, dtype=torch.float32, device=self.device)
+        # gradient exchange overlapped with backward (set per call by train_microbatch(overlap=...))
+        self._ov = None
+        self._ov_trigger: Dict[str, object] = {}
+        self._comm_stream = None
+        self._ov_events: List[object] = []
 
     # -- helpers -------------------------------------------------------------------------------
     def _new(self, *shape, dtype=None):
@@ -207,7 +212,9 @@ class NativeEngine:
             Fn.conv3x3_wgrad(st.x, st.dy, self.stem_dw, impl=self.conv_impl)
             dw.add_(self.stem_dw[..., :dw.shape[3]])
         else:
+            bucket = self._arm(sp.name + ".weight", sp.cin, sp.cout)
             Fn.conv3x3_wgrad(st.x, st.dy, dw, impl=self.conv_impl)
+            self._bucket_done(bucket)
         if need_dx and st.dx is not None:
             w_lp = self._w3(self.flat_lp, sp.name + ".weight")
             if colsum:
@@ -262,6 +269,59 @@ class NativeEngine:
             Fn.head_ce_fwd_bwd(self.head_in, wh, bh, self.labels, 0.0, None, None, None,
                                self.pred, self.loss_acc)
 
+    # -- exchange under backward (parallel/overlap.py, csrc/comm/overlap.cu) ----------------------------
+    def _begin_overlap(self, ov) -> None:
+        """``ov``: ``parallel.symm.SymmetricAllReduce`` after ``setup_overlap`` (or None)."""
+        self._ov = ov
+        if ov is None:
+            return
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(self.device)
+            self._ov_events = [torch.cuda.Event() for _ in range(len(ov.ovl_buckets) + 1)]
+        self._ov_trigger = {b.trigger: b for b in ov.ovl_buckets if b.trigger is not None}
+        import os
+        self._ov_armed = (Fn._conv_impl(self.conv_impl) != "cudnn" and
+                          os.environ.get("B200SEG_WGRAD", "tcgen05") != "cudnn")
+
+    def _arm(self, param_name: str, cin: int, cout: int):
+        """Before the wgrad call that completes a bucket: make its last kernel the all-reduce trigger."""
+        if self._ov is None:
+            return None
+        b = self._ov_trigger.get(param_name)
+        if b is None:
+            return None
+        armed = self._ov_armed and Fn._use_tc(cin, cout, self.conv_impl)
+        if armed:
+            torch.ops.b200seg.arm_next_wgrad(self._ov.arm_ptr(b.index))
+        return (b, armed)
+
+    def _bucket_done(self, armed_bucket) -> None:
+        if armed_bucket is None:
+            return
+        b, armed = armed_bucket
+        if armed:
+            torch.ops.b200seg.arm_next_wgrad(0)             # never leave a stale trigger behind
+        self._queue_reduce(b, self_publish=not armed)
+
+    def _queue_reduce(self, b, self_publish: bool) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        ev = self._ov_events[b.index]
+        ev.record(cur)                                      # the bucket's producers are all queued before this
+        self._comm_stream.wait_event(ev)
+        with torch.cuda.stream(self._comm_stream):
+            self._ov.reduce_bucket(b, self_publish)
+
+    def _end_overlap(self) -> None:
+        """The final bucket (first encoder block, BN / bias / stem / head gradients), then join."""
+        ov = self._ov
+        if ov is None:
+            return
+        self._queue_reduce(ov.ovl_buckets[-1], self_publish=True)
+        done = self._ov_events[-1]
+        done.record(self._comm_stream)
+        torch.cuda.current_stream(self.device).wait_event(done)
+        self._ov = None
+
     @torch.no_grad()
     def backward(self) -> None:
         for i in (1, 2, 3, 4, 5):
@@ -276,9 +336,11 @@ class NativeEngine:
                 Fn.upsample_bilinear2x_bwd(d_up, d_below)
             else:
                 name = f"up_conv{i}.up_sample"
+                bucket = self._arm(name + ".weight", self.c_up[i], self.c_up[i])
                 Fn.convT2x2_bwd(below, d_up, self._params[name + ".weight"], self._convT_lp(name),
                                 self._params[name + ".weight"].grad,
                                 self._seg(self.flat_g, name + ".bias"), d_below, d_up_partials=part)
+                self._bucket_done(bucket)
         s0, s1 = self.stages["double_conv"]
         self._stage_bwd(s1)
         self._stage_bwd(s0)
@@ -288,17 +350,24 @@ class NativeEngine:
             self._stage_bwd(s0, need_dx=(i != 1))
 
     @torch.no_grad()
-    def train_microbatch(self, loss_scale: Optional[float] = None) -> torch.Tensor:
+    def train_microbatch(self, loss_scale: Optional[float] = None, overlap=None) -> torch.Tensor:
         """Forward + loss + backward on the batch already in ``x_in`` / ``labels``.
 
         Gradients are ACCUMULATED into the flat gradient buffer (R:756 semantics).  Returns the
         device tensor ``[loss_sum, correct]`` (read it back only when logging).
+
+        ``overlap``: the symmetric-memory reducer; when given, this micro-batch ends an accumulation
+        window and the gradient buckets are all-reduced across ranks while backward runs (each
+        bucket's reduction is triggered by the wgrad kernel that completes it).  On return the
+        flat gradient buffer holds the SUM over ranks, bit-identical everywhere (R:402-433).
         """
         self.training = True
         pixels = self.N * self.H * self.W
         self.forward()
         self._head(True, (1.0 / pixels) if loss_scale is None else loss_scale)
+        self._begin_overlap(overlap)
         self.backward()
+        self._end_overlap()
         return self.loss_acc
 
     @torch.no_grad()

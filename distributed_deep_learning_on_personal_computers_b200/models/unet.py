@@ -167,7 +167,7 @@ class UNet(nn.Module):
         tensor-core wgrad kernels write (everything but the 3-channel stem and the 1x1 head) — in
         ``parameters()`` order (the reference's wire order, R:453), then all the small tensors (BN
         affine, biases, stem, head).  The split lets the fused exchange treat the two regions
-        differently (``parallel/allreduce.py``).  Returns ``{"param", "grad", "offsets", "bulk_elems"}``;
+        differently (``parallel/allreduce.py``).  Returns ``{"param", "grad", "offsets", "bulk_elems", "bulk_names"}``;
         ``offsets[name] = (start, numel)`` in elements.  Nothing depends on the order: every consumer
         goes through ``offsets`` and checkpoints are by name.
         """
@@ -184,10 +184,13 @@ class UNet(nn.Module):
         offsets: "OrderedDict[str, Tuple[int, int]]" = OrderedDict()
         total = 0
         bulk_elems = 0
+        bulk_names = set()
         for want_bulk in (True, False):
             for name, p in params:
                 if is_bulk(name, p) != want_bulk:
                     continue
+                if want_bulk:
+                    bulk_names.add(name)
                 offsets[name] = (total, p.numel())
                 total += (p.numel() + FLAT_ALIGN - 1) // FLAT_ALIGN * FLAT_ALIGN
             if want_bulk:
@@ -204,7 +207,8 @@ class UNet(nn.Module):
                 p.grad = self._internal_view(flat_g, off, p, is_t)
         for _, buf in self.named_buffers():
             buf.data = buf.data.to(device)
-        self._flat = {"param": flat_p, "grad": flat_g, "offsets": offsets, "bulk_elems": bulk_elems}
+        self._flat = {"param": flat_p, "grad": flat_g, "offsets": offsets, "bulk_elems": bulk_elems,
+                      "bulk_names": bulk_names}
         return self._flat
 
     @property

@@ -122,6 +122,69 @@ class SymmetricAllReduce:
         torch.cuda.synchronize(dev)
         dist.barrier(device_ids=[dev.index])
 
+    # -- exchange overlapped with backward (csrc/comm/overlap.cu) ------------------------------------
+    def setup_overlap(self, buckets, timeout_s: float = 30.0, blocks: int = 0) -> None:
+        """Allocate the bucket signal pad (symmetric), the local exchange state and one ``GradArm`` per
+        bucket.  ``buckets``: ``parallel.overlap.plan_buckets`` output for THIS buffer."""
+        import os
+        import torch.distributed._symmetric_memory as symm_mem
+        ops = torch.ops.b200seg
+        if self.codec.name != "fp32":
+            raise RuntimeError("the overlapped exchange reduces fp32 gradients in place; use codec fp32")
+        if len(buckets) > ops.overlap_max_buckets():
+            raise ValueError("too many buckets")
+        dev = self.buffer.device
+        world, rank = self.ctx.world_size, self.ctx.rank
+        self.ovl_pad = symm_mem.empty(int(ops.overlap_pad_words()), dtype=torch.int32, device=dev)
+        self.ovl_pad.zero_()
+        self.h_ovl = symm_mem.rendezvous(self.ovl_pad, self.group)
+        self.ovl_pad_ptrs = [int(p) for p in self.h_ovl.buffer_ptrs]
+        # local state: [0] exchange number, [1] CTA counter of the final kernel, [2 + b] arrival counter of bucket b
+        self.ovl_state = torch.zeros(2 + len(buckets), dtype=torch.int32, device=dev)
+        self.ovl_state[0] = 1
+        base = self.ovl_state.data_ptr()
+        arms = torch.zeros(len(buckets), 19, dtype=torch.int64)
+        for b in buckets:
+            arms[b.index, 0] = base + 4 * (2 + b.index)
+            arms[b.index, 1] = base
+            for r in range(world):
+                arms[b.index, 2 + r] = self.ovl_pad_ptrs[r] + 4 * int(ops.overlap_flag_index(b.index, rank))
+            arms[b.index, 18] = world                      # int world + 4 bytes of padding (little endian)
+        self.ovl_arms = arms.to(dev)
+        self.ovl_buckets = list(buckets)
+        self.ovl_timeout_s = float(timeout_s)
+        self.ovl_blocks = int(blocks or os.environ.get("B200SEG_OVL_BLOCKS", "16"))
+        self.ovl_abort_index = int(ops.overlap_abort_index())
+        torch.cuda.synchronize(dev)
+        dist.barrier(device_ids=[dev.index])
+
+    def arm_ptr(self, bucket_index: int) -> int:
+        return self.ovl_arms.data_ptr() + 19 * 8 * bucket_index
+
+    @torch.no_grad()
+    def reduce_bucket(self, bucket, self_publish: bool) -> None:
+        """Queue the reduction of one bucket on the CURRENT stream (the engine runs it on its side stream)."""
+        from ..ops import functional as Fn
+        offs = [o for o, _ in bucket.ranges]
+        cnts = [n for _, n in bucket.ranges]
+        torch.ops.b200seg.bucket_reduce(self.multicast_ptr, [] if self.multicast_ptr else self.grad_ptrs,
+                                        self.ovl_pad_ptrs, self.ovl_state, self.ctx.rank, bucket.index,
+                                        bool(self_publish or bucket.final), bool(bucket.final), offs, cnts, 1.0,
+                                        self.ovl_timeout_s, self.ovl_blocks)
+        Fn._tick()
+
+    def check_abort(self) -> None:
+        """Raise ``PeerLost`` if a bounded wait on the device gave up (synchronizes the device)."""
+        pad = getattr(self, "ovl_pad", None)
+        if pad is None:
+            return
+        torch.cuda.synchronize(pad.device)
+        word = int(pad[self.ovl_abort_index].item()) & 0xFFFFFFFF
+        if word:
+            from .star import PeerLost
+            raise PeerLost(f"gradient exchange timed out on rank {word & 0xFFFF} after {self.ovl_timeout_s:.0f} s "
+                           "(a peer did not publish its bucket); the step's gradients are not reduced")
+
     @property
     def multicast_supported(self) -> bool:
         try:
@@ -177,6 +240,15 @@ class SymmetricAllReduce:
         torch.ops.b200seg.peer_barrier(self.sig_ptrs, self.ctx.rank, self.epoch)
         self.epoch += 1
         Fn._tick()
+
+    def suspend_fused(self) -> None:
+        """Fused mode: stop the wgrad launchers from adding through the multicast alias (graph warm-up)."""
+        if self.fused_bulk:
+            torch.ops.b200seg.set_grad_multicast(self.buffer_full, 0, 0)
+
+    def resume_fused(self) -> None:
+        if self.fused_bulk:
+            torch.ops.b200seg.set_grad_multicast(self.buffer_full, self.fused_bulk, self.multicast_ptr)
 
     def close(self) -> None:
         if self.fused_bulk:

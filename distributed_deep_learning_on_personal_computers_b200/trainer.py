@@ -35,7 +35,7 @@ from .parallel.allreduce import GradientSynchronizer
 from .utils import checkpoint as ckpt
 from .utils.data import PinnedBatchLoader, RankSampler, TileSet, build_datasets
 from .utils.metrics import DeviceMeter, RunLog, dump_samples
-from .utils.timing import PhaseTimer
+from .utils.timing import PhaseTimer, nvtx_range
 
 
 class Trainer:
@@ -70,6 +70,18 @@ class Trainer:
                              "(they are what performs the reduction)")
         self.engine: Optional[NativeEngine] = None
         self._engine_shape = None
+        # Default on a multi-GPU node: the exchange runs UNDER backward, bucket by bucket, triggered by the
+        # wgrad kernels (parallel/overlap.py); no whole-buffer all-reduce follows the backward pass.
+        self.overlap = None
+        nat = self.sync.native
+        if (cfg.overlap and nat is not None and not self.sync.fused and self.sync.codec.name == "fp32"
+                and self.engine_kind == "native" and not cfg.requantize_output):
+            from .parallel.overlap import backward_order, plan_buckets
+            buckets = plan_buckets(self.model.flat["offsets"], backward_order(self.model),
+                                   self.model.flat["grad"].numel(), cfg.bucket_mb)
+            nat.setup_overlap(buckets, timeout_s=cfg.timeout_s)
+            self.overlap = nat
+        self._reduced = False         # the pending gradients were already all-reduced under backward
         self.optimizer = build_optimizer(self.model, cfg)
         self.optimizer.rebind_grad(self.model.flat["grad"])
 
@@ -83,8 +95,7 @@ class Trainer:
         self.epoch = 0
         self.global_step = 0          # micro-batches seen
         self.pending = 0              # micro-batches accumulated since the last exchange
-        self._graph = None
-        self._graph_launches = 0
+        self._graphs = {}             # (reduce under backward?) -> (CUDAGraph, launches)
         if cfg.resume:
             self.resume(cfg.resume)
 
@@ -118,44 +129,80 @@ class Trainer:
             self.engine = NativeEngine(self.model, n, h, w)
             self._engine_shape = (n, h, w)
             self.optimizer.attach_lowp(self.engine.flat_lp)
-            self._graph = None
+            self._graphs = {}
         return self.engine
 
     # -- one micro-batch ---------------------------------------------------------------------------
-    def micro_step(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> torch.Tensor:
-        """Forward + loss + backward; gradients accumulate. Returns device ``[loss_sum, correct]``."""
+    def micro_step(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, sync_now: bool = False) -> torch.Tensor:
+        """Forward + loss + backward; gradients accumulate. Returns device ``[loss_sum, correct]``.
+
+        ``sync_now``: this micro-batch ends an accumulation window.  With the overlapped exchange (the
+        default on a multi-GPU node) its backward then also all-reduces the gradient buckets across ranks,
+        and the following ``sync_and_step`` only steps the optimizer.
+        """
         n, h, w, _ = images_u8.shape
         if self.engine_kind == "torch":
             return self._micro_step_autograd(images_u8, labels_u8)
         eng = self._ensure_engine(n, h, w)
         eng.load_batch(images_u8, labels_u8)
+        ov = self.overlap if sync_now else None
         use_graph = self.cfg.cuda_graph and self.device.type == "cuda"
         if not use_graph:
-            return eng.train_microbatch()
-        if self._graph is None:
-            # warm-up on a side stream (allocator, lazy module loads), then capture once
-            s = torch.cuda.Stream(self.device)
-            s.wait_stream(torch.cuda.current_stream(self.device))
-            saved = self.model.flat["grad"].clone()
-            bufs = [b.clone() for b in self.model.buffers()]
-            with torch.cuda.stream(s):
-                eng.train_microbatch()
-            torch.cuda.current_stream(self.device).wait_stream(s)
-            self.model.flat["grad"].copy_(saved)                 # undo the warm-up's side effects
-            for b, keep in zip(self.model.buffers(), bufs):
-                b.copy_(keep)
-            before = Fn.launch_count()
-            self._graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self._graph):
-                eng.train_microbatch()
-            self._graph_launches = Fn.launch_count() - before
-            self.model.flat["grad"].copy_(saved)
-            for b, keep in zip(self.model.buffers(), bufs):
-                b.copy_(keep)
-            Fn._tick(-self._graph_launches)
-        self._graph.replay()
-        Fn._tick(self._graph_launches)
+            out = eng.train_microbatch(overlap=ov)
+            self._reduced = ov is not None
+            return out
+        key = ov is not None
+        if key not in self._graphs:
+            self._graphs[key] = self._capture(eng, ov)
+        graph, launches = self._graphs[key]
+        with nvtx_range("micro_batch_graph"):
+            graph.replay()
+        Fn._tick(launches)
+        self._reduced = ov is not None
         return eng.loss_acc
+
+    def _capture(self, eng: NativeEngine, ov):
+        """Warm up on a side stream (allocator, lazy module loads), then capture one micro-batch.
+
+        The warm-up never touches the fabric: it runs without the overlapped exchange and, in fused mode,
+        with the multicast alias unregistered -- a warm-up that added into the peers' buffers would race
+        with their own restore of the saved gradients and leave the replicas diverged for good."""
+        flat_g = self.model.flat["grad"]
+        s = torch.cuda.Stream(self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        saved = flat_g.clone()
+        bufs = [b.clone() for b in self.model.buffers()]
+        fused = self.sync.fused and self.sync.native is not None
+        if fused:
+            self.sync.native.suspend_fused()
+        with torch.cuda.stream(s):
+            eng.train_microbatch()
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        if fused:
+            self.sync.native.resume_fused()
+        flat_g.copy_(saved)                                  # undo the warm-up's side effects
+        for b, keep in zip(self.model.buffers(), bufs):
+            b.copy_(keep)
+        before = Fn.launch_count()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            eng.train_microbatch(overlap=ov)
+        launches = Fn.launch_count() - before
+        flat_g.copy_(saved)
+        for b, keep in zip(self.model.buffers(), bufs):
+            b.copy_(keep)
+        Fn._tick(-launches)
+        return graph, launches
+
+    def train_step(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> torch.Tensor:
+        """One full data-parallel step (sync every micro-batch): forward, loss, backward with the
+        gradient exchange running under it, optimizer.  Returns device ``[loss_sum, correct]``."""
+        out = self.micro_step(images_u8, labels_u8, sync_now=True)
+        self.pending += 1
+        self.global_step += 1
+        self.sync_and_step()
+        return out
 
     def _micro_step_autograd(self, images_u8, labels_u8) -> torch.Tensor:
         """Stock-PyTorch path (eager autograd, as the reference's R:754-756), for comparison."""
@@ -176,14 +223,37 @@ class Trainer:
     # -- exchange + step --------------------------------------------------------------------------
     def sync_and_step(self) -> None:
         k = max(self.pending, 1)
-        with self.timer.phase("sync"):
-            scale = self.sync.sync(k)
-        with self.timer.phase("optimizer"):
+        with self.timer.phase("sync"), nvtx_range("gradient_exchange"):
+            if self._reduced:                       # already all-reduced under the backward pass
+                scale = self.sync._post_scale(k)
+                self._reduced = False
+            else:
+                scale = self.sync.sync(k)
+        with self.timer.phase("optimizer"), nvtx_range("optimizer"):
             self.optimizer.step(grad_scale=scale, zero_grad=True)
             if self.engine is not None and self.optimizer.p_lowp is None:
                 self.engine.refresh_lowp()
             self.sync.after_step()
         self.pending = 0
+
+    def check_peers(self) -> None:
+        """Raise ``PeerLost`` if a bounded device-side wait of the gradient exchange gave up (a peer stalled
+        or died; the reference would hang forever in ``recv``, R:98).  Rank 0 first writes
+        ``<out_dir>/abort.pt`` so the run can be resumed (``--resume``).  Synchronizes the device: called at
+        epoch boundaries and every ``check_peers_every`` steps, not per step."""
+        nat = getattr(self.sync, "native", None)
+        if nat is None:
+            return
+        from .parallel.star import PeerLost
+        try:
+            nat.check_abort()
+        except PeerLost:
+            if self.ctx.is_coordinator:
+                try:
+                    self.save(os.path.join(self.cfg.out_dir, "abort.pt"))
+                except Exception:                      # the abort must surface even if the disk is full
+                    pass
+            raise
 
     # -- epochs --------------------------------------------------------------------------------------
     def train_epoch(self) -> Dict[str, float]:
@@ -195,17 +265,20 @@ class Trainer:
         it = 0
         for images, labels in self.loader.batches(order):
             with self.timer.phase("micro_batch"):
-                out = self.micro_step(images, labels)
+                out = self.micro_step(images, labels, sync_now=((it + 1) % cfg.sync_every == 0))
             self.meter.add(out, labels.numel())
             it += 1
             self.pending += 1
             self.global_step += 1
             if it % cfg.sync_every == 0:                           # R:759
                 self.sync_and_step()
+                if cfg.check_peers_every and (self.global_step // cfg.sync_every) % cfg.check_peers_every == 0:
+                    self.check_peers()
             if cfg.max_steps and self.global_step >= cfg.max_steps:
                 break
         if self.pending and cfg.flush_at_epoch_end:                 # Q7
             self.sync_and_step()
+        self.check_peers()
         stats = self.meter.read()
         tm = self.timer.summary()
         stats.update(epoch=self.epoch, epoch_s=time.perf_counter() - t_epoch,

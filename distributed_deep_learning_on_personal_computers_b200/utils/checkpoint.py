@@ -33,8 +33,13 @@ def save(path: str, model, optimizer, epoch: int, step: int, config: Dict,
     return path
 
 
-def load(path: str, model, optimizer=None, map_location="cpu") -> Dict:
-    ckpt = torch.load(path, map_location=map_location, weights_only=False)
+def load(path: str, model, optimizer=None, map_location="cpu", trusted: bool = False) -> Dict:
+    """``trusted=False`` (default) uses torch's restricted unpickler: a checkpoint holds only tensors, dicts,
+    lists, tuples and scalars, so nothing else needs to be constructible from the file (the star transport
+    avoids pickle for the same reason).  ``trusted=True`` (or ``B200SEG_TRUSTED_CHECKPOINT=1``) falls back
+    to the full unpickler for files written by other tools."""
+    trusted = trusted or os.environ.get("B200SEG_TRUSTED_CHECKPOINT") == "1"
+    ckpt = torch.load(path, map_location=map_location, weights_only=not trusted)
     with torch.no_grad():
         own = model.state_dict()
         missing = [k for k in own if k not in ckpt["model"]]

@@ -63,3 +63,19 @@ class PhaseTimer:
         self.resolve()
         self.totals_ms.clear()
         self.counts.clear()
+
+
+@contextmanager
+def nvtx_range(name: str):
+    """NVTX range around a phase of the step (visible in Nsight Systems / ncu --nvtx); a no-op without CUDA.
+
+    The reference marks its phases with ``print(time.time() - start)`` pairs (R:265, R:317, R:322, R:388,
+    R:397, R:440); these are the same phases as ranges a profiler can attribute kernels to."""
+    on = torch.cuda.is_available()
+    if on:
+        torch.cuda.nvtx.range_push(name)
+    try:
+        yield
+    finally:
+        if on:
+            torch.cuda.nvtx.range_pop()

@@ -136,6 +136,31 @@ int b200seg_barrier(unsigned int* const* signal_ptrs, int rank, int world, unsig
 int b200seg_set_grad_multicast(const void* local_base, long long bytes, const void* multicast_base);
 long long b200seg_grad_multicast_delta(const void* p);
 
+/* ---- gradient exchange overlapped with backward (csrc/comm/overlap.cu): replaces the strictly-after-
+ * backward round of R:756-763 -> R:255-440 / R:443-556.  The flat gradient buffer is reduced bucket by
+ * bucket while later layers still compute.
+ *  b200seg_arm_next_wgrad: the LAST kernel launched by the next b200conv_wgrad / b200conv_convT_wgrad
+ *    call becomes the bucket's trigger: its last CTA stores the exchange number into flags[bucket][rank]
+ *    of every rank's pad.  `arm` is a device pointer to {u32* counter; const u32* epoch;
+ *    u32* peer_flag[16]; int world; int pad;} (all device addresses); NULL disarms.
+ *  b200seg_bucket_reduce: waits until every rank has published the bucket, then reduces it in place
+ *    (rank r owns slice r of every range): NVLS through `multicast_ptr`, or peer loads / stores over
+ *    `grad_ptrs` when multicast_ptr is NULL.  offs / counts are in floats (multiples of 4), up to 4
+ *    ranges.  `state` = local device u32[2] {exchange number (start at 1), CTA counter (0)}.
+ *    self_publish: the kernel publishes the bucket flag itself (no arming wgrad launch).  final: last
+ *    bucket of the exchange: ends with a cross-rank "done" exchange and advances the exchange number.
+ *    Waits are bounded by timeout_s; on expiry the abort word (b200seg_overlap_abort_index()) is raised in
+ *    every rank's pad and the kernels return without reducing. */
+void b200seg_arm_next_wgrad(const void* arm);
+int b200seg_overlap_pad_words(void);
+int b200seg_overlap_max_buckets(void);
+int b200seg_overlap_flag_index(int bucket, int rank);
+int b200seg_overlap_abort_index(void);
+int b200seg_bucket_reduce(float* multicast_ptr, float* const* grad_ptrs, unsigned int* const* pad_ptrs,
+                          unsigned int* state, int rank, int world, int bucket, int self_publish, int final,
+                          int n_ranges, const long long* offs, const long long* counts, float post_scale,
+                          double timeout_s, int blocks, cudaStream_t st);
+
 #ifdef __cplusplus
 }
 #endif

@@ -211,3 +211,142 @@ def test_fused_wgrad_allreduce_matches_local_plus_nccl(tmp_path):
     assert res["losses"][-1] < res["losses"][0]
     s = res["param_sums"]
     assert max(s) - min(s) <= 1e-6 * max(abs(s[0]), 1.0), s        # replicas agree to rounding
+
+
+def _overlap_worker(rank, world, port, graph, q, out_dir):
+    """The default exchange (buckets reduced under backward, triggered by the wgrad kernels) against the
+    same micro-batch accumulated locally and summed by NCCL; replicas must hold identical bits."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
+    from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
+    cfg = TrainConfig(base_channels=32, tile=128, train_tiles=4 * world, holdout_tiles=0, batch_size=2, sync_every=1,
+                      epochs=1, codec="fp32", comm="auto", device="cuda", out_dir=out_dir, sample_images=0,
+                      cuda_graph=graph, bucket_mb=1.0, timeout_s=60).apply_env()
+    tr = Trainer(cfg)
+    res = {"overlap": tr.overlap is not None, "backend": tr.sync.backend,
+           "buckets": len(tr.overlap.ovl_buckets) if tr.overlap is not None else 0,
+           "multicast": bool(tr.sync.native.multicast_ptr) if tr.sync.native else False}
+    tiles = synthetic_tiles(2, 128, 6, 10 + rank)
+    img, lab = tiles.images.cuda(), tiles.labels.cuda()
+    errs, same = [], []
+    for rep in range(4):
+        tr.sync.flat.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        tr.micro_step(img, lab, sync_now=True)               # backward + bucketed exchange
+        assert tr._reduced
+        tr._reduced = False
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        g_ovl = tr.sync.flat.clone()
+        tr.sync.flat.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[rank])
+        tr.micro_step(img, lab, sync_now=False)              # local accumulation only
+        g_ref = tr.sync.flat.clone()
+        dist.all_reduce(g_ref)
+        scale = g_ref.abs().max().item()
+        errs.append(((g_ovl - g_ref).abs().max().item(), scale))
+        lst = [torch.empty_like(g_ovl) for _ in range(world)]
+        dist.all_gather(lst, g_ovl)
+        same.append(all(torch.equal(lst[0], t) for t in lst))
+    res["errs"], res["same"] = errs, same
+    tr.sync.flat.zero_()
+    torch.cuda.synchronize()
+    dist.barrier(device_ids=[rank])
+    losses = []
+    for _ in range(3):
+        losses.append(tr.train_epoch()["mean_loss"])
+        tr.epoch += 1
+    tr.overlap.check_abort()
+    chk = tr.model.flat["param"].double().sum().reshape(1)
+    lst = [torch.zeros_like(chk) for _ in range(world)]
+    dist.all_gather(lst, chk)
+    res["losses"] = losses
+    res["param_sums"] = [t.item() for t in lst]
+    if rank == 0:
+        q.put(res)
+    tr.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("graph", [False, True])
+def test_overlapped_exchange_matches_nccl_and_replicas_identical(graph, tmp_path):
+    world = min(torch.cuda.device_count(), 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_overlap_worker, args=(r, world, port, graph, q, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    print(res)
+    assert res["overlap"] and res["backend"] == "native" and res["buckets"] >= 3
+    for err, scale in res["errs"]:
+        assert err <= 2e-4 * scale + 1e-6, res["errs"]       # wgrad accumulation order differs run to run
+    assert all(res["same"]), "replicas must hold identical bits after the exchange (R:402-433)"
+    assert res["losses"][-1] < res["losses"][0]
+    s = res["param_sums"]
+    assert max(s) == min(s), s                                 # bit-identical replicas after training
+
+
+def _peer_loss_worker(rank, world, port, q, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import time
+    from distributed_deep_learning_on_personal_computers_b200 import TrainConfig
+    from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    from distributed_deep_learning_on_personal_computers_b200.parallel.star import PeerLost
+    from distributed_deep_learning_on_personal_computers_b200.utils.data import synthetic_tiles
+    cfg = TrainConfig(base_channels=32, tile=64, train_tiles=8, holdout_tiles=0, batch_size=2, sync_every=1,
+                      epochs=1, codec="fp32", comm="auto", device="cuda", out_dir=out_dir, sample_images=0,
+                      cuda_graph=False, timeout_s=4).apply_env()
+    tr = Trainer(cfg)
+    tiles = synthetic_tiles(2, 64, 6, rank)
+    img, lab = tiles.images.cuda(), tiles.labels.cuda()
+    tr.train_step(img, lab)
+    tr.check_peers()
+    out = {"rank": rank}
+    if rank == 0:
+        t0 = time.perf_counter()
+        tr.train_step(img, lab)                       # rank 1 never joins this exchange
+        try:
+            tr.check_peers()
+            out["raised"] = False
+        except PeerLost as exc:
+            out["raised"] = True
+            out["msg"] = str(exc)
+        out["seconds"] = time.perf_counter() - t0
+        path = os.path.join(out_dir, "abort.pt")
+        out["ckpt"] = os.path.exists(path)
+        q.put(out)
+    else:
+        time.sleep(12)                                # a stalled peer
+    os._exit(0)                                       # the process group is beyond a clean shutdown
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_stalled_peer_raises_peer_lost_and_leaves_a_checkpoint(tmp_path):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_loss_worker, args=(r, world, port, q, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+    assert res["raised"], res
+    assert res["seconds"] < 4 + 5, res
+    assert res["ckpt"], "rank 0 must leave a checkpoint behind"
+    from distributed_deep_learning_on_personal_computers_b200.utils import checkpoint as ckpt
+    import torch as _t
+    state = _t.load(os.path.join(str(tmp_path), "abort.pt"), weights_only=True)
+    assert "model" in state and "optimizer" in state
