@@ -326,6 +326,8 @@ def _peer_loss_worker(rank, world, port, q, out_dir):
         path = os.path.join(out_dir, "abort.pt")
         out["ckpt"] = os.path.exists(path)
         q.put(out)
+        q.close()
+        q.join_thread()                               # flush the feeder thread before the hard exit below
     else:
         time.sleep(12)                                # a stalled peer
     os._exit(0)                                       # the process group is beyond a clean shutdown
