@@ -990,6 +990,19 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
 
 // =================================================================================================
 // Host side
+
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+// GPU's memory hung the GPU.  Operands of the cluster launches are activations and weights that the
+// engine allocates locally; a pointer that is not plain device memory of the CURRENT device (a peer
+// mapping, an IPC or cuMemMap'd range owned by another GPU, host memory) takes the non-multicast kernel.
+static bool local_device_memory(const void* p) {
+  cudaPointerAttributes a{};
+  int dev = -1;
+  if (p == nullptr || cudaGetDevice(&dev) != cudaSuccess) return false;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice && a.device == dev;
+}
+
 static int ilog2_floor(int x) { int l = 0; while ((2 << l) <= x) ++l; return l; }
 
 struct TileGeom { int tw_log2, th_log2, tn, tiles_w, tiles_h, tiles_g; };
@@ -1181,7 +1194,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   // Kept as an opt-in experiment (profiles/variants_in_situ.txt).
   p.cluster = 1;
   if (kClusterSize == 2 && cluster_env() && mode != 2 && mode != 3 && p.m_tiles >= 2 * kNumSMs && (p.block_n % 32 == 0) &&
-      (bmn ? true : (p.block_n / 2) % 8 == 0))
+      (bmn ? true : (p.block_n / 2) % 8 == 0) && !dry && local_device_memory(w))
     p.cluster = 2;
   const int unit = p.n_tiles * p.cluster;
   int grid = kNumSMs - (kNumSMs % unit);
@@ -1381,7 +1394,7 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   static int wcl_env = -1;
   if (wcl_env < 0) { const char* e = getenv("B200SEG_WGRAD_CLUSTER"); wcl_env = (e == nullptr) ? 2 : (e[0] == '0' ? 0 : (e[0] == '4' ? 4 : 2)); }
   const int nbt = p.quads * nblocks;
-  if (wcl_env && p.m_tiles % 2 == 0 && nbt % 2 == 0) {
+  if (wcl_env && p.m_tiles % 2 == 0 && nbt % 2 == 0 && local_device_memory(x) && local_device_memory(dy)) {
     const bool quad = wcl_env == 4 && p.quads == 1 && p.n_tiles % 2 == 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(base_items * ks);
