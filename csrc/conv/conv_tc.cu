@@ -65,6 +65,7 @@ struct TapGemmParams {
   int rows2;                       // STRIP mode: a work unit is TWO vertically adjacent row tiles sharing every weight tile
   int rows4;                       // STRIP mode, resident bank, N = 64: FOUR-row units, vertical taps merged along N
   int reg_stats;                   // N = 64: BN statistics accumulated in registers (B200SEG_REG_STATS=0 disables)
+  int epi_private;                 // STRIP, N = 64: warp-private epilogue pipelines (no CTA-wide barriers), stores through map_o2
   int b_resident;                  // STRIP mode: all 9 * kc weight tiles stay in smem for the whole kernel
   int xslots;                      // STRIP mode: number of input-strip slots
   uint32_t xslot_bytes;            // STRIP mode: bytes per strip slot (130 rows x 128 B, padded)
@@ -101,7 +102,8 @@ __device__ __forceinline__ void named_bar_sync(int id, int n) {
 template <int BLOCK_K, bool B_MN, bool STRIP>
 __global__ void __launch_bounds__(kTapThreads, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                const __grid_constant__ CUtensorMap map_o, const TapGemmParams p) {
+                const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_o2,
+                const TapGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + (size_t)p.stages * p.stage_bytes + (STRIP ? (size_t)p.xslots * p.xslot_bytes : 0);
@@ -136,6 +138,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
+    tma_prefetch_desc(&map_o2);
     for (int s = 0; s < p.stages && s < kMaxStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], csz); }
     for (int s = 0; s < 4; ++s) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], kEpiThreads); }
     for (int s = 0; s < kMaxXSlots; ++s) { mbar_init(&bar_xfull[s], 1); mbar_init(&bar_xempty[s], 1); }
@@ -496,6 +499,125 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }   // elect_one
   } else {
     // ===================================== epilogue ==========================================
+    if (STRIP && p.epi_private) {
+      // Warp-private pipelines for the 64-column strip layers.  ncu showed the shared epilogue below taking
+      // ~2300 cycles per 128 x 64 tile, most of it in its two CTA-wide barriers and in all 256 threads
+      // waiting for one thread's TMA store (profiles/ncu_mma_issue.txt).  Here warp (q, half) owns rows
+      // 32q..32q+31 x columns 32half..32half+31 of every tile: it reads its TMEM block, packs it into its
+      // OWN 2 KB slab (two slabs, double-buffered) and its lane 0 issues its own 32-pixel x 32-channel TMA
+      // store.  Nothing is shared between warps until the statistics are folded at the very end.
+      const int q = warp & 3, half = (warp - 2) >> 2;
+      uint8_t* const slab0 = staging + (size_t)(warp - 2) * 4096;
+      const uint32_t slab_a = smem_u32(slab0) + lane * 64;
+      const uint32_t a_tfull = smem_u32(bar_tfull);
+      const bool stats = p.partials != nullptr;
+      const bool has_bias = p.bias != nullptr;
+      float rs_s[32], rs_q[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) rs_s[j] = rs_q[j] = 0.f;
+      int acc = 0, buf = 0;
+      uint32_t acc_phase = 0;
+      const int acc_n = p.rows2 ? 4 : 2;
+      const int acc_cols = p.rows2 ? 128 : 256;
+      const int subs = p.rows4 ? 4 : (p.rows2 ? 2 : 1);
+      const int sh = p.rows4 ? 2 : (p.rows2 ? 1 : 0);
+      const int n_units = p.m_tiles >> sh;
+      const int hp_n = p.H >> sh;
+      const int ch0 = half * 32;
+      for (int mu = m_first; mu < n_units; mu += m_step) {
+        // tile coordinates, off the critical path (needed by lane 0 only; computed before the wait)
+        const int w0 = ((mu % p.tiles_w) << p.tw_log2) + q * 32;
+        const int hb = ((mu / p.tiles_w) % hp_n) << sh;
+        const int n0 = mu / (p.tiles_w * hp_n);
+#pragma unroll 1
+        for (int sub = 0; sub < subs; ++sub) {
+          if (!p.rows4 || sub == 0) {
+            mbar_wait_a(a_tfull + 8 * acc, acc_phase);
+            tc_fence_after();
+          }
+          const uint32_t t_addr = tmem_base + acc * acc_cols + (p.rows4 ? sub * 64 : 0) +
+                                  (static_cast<uint32_t>(q * 32) << 16) + ch0;
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(t_addr, r);
+          tmem_ld_wait();
+          tc_fence_before();
+          if (!p.rows4 || sub == 3) {
+            mbar_arrive(&bar_tempty[acc]);                  // accumulator drained (it is in registers now)
+            if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
+          }
+          if (has_bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + s_bias[ch0 + j]);
+          }
+          if (stats) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = __uint_as_float(r[j]);
+              rs_s[j] += v;
+              rs_q[j] = fmaf(v, v, rs_q[j]);
+            }
+          }
+          const uint32_t dst = slab_a + buf * 2048;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            float f[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+            const bf16x8 pk = pack8(f);
+            const uint32_t* pw = reinterpret_cast<const uint32_t*>(&pk);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + v * 16), "r"(pw[0]), "r"(pw[1]),
+                         "r"(pw[2]), "r"(pw[3])
+                         : "memory");
+          }
+          fence_proxy_async();                              // slab writes -> visible to TMA
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(&map_o2, slab0 + buf * 2048, n_tile * 64 + ch0, w0, hb + sub, n0);
+            tma_store_commit();
+            tma_store_wait_read<1>();                       // the slab written NEXT (stored one tile ago) is free
+          }
+          __syncwarp();
+          buf ^= 1;
+        }
+      }
+      if (lane == 0) tma_store_wait_read<0>();
+      if (stats) {
+        // fold the 128 rows: butterfly inside each warp, then the four warps of a column half through smem
+        named_bar_sync(1, kEpiThreads);                     // every slab is free (they are the scratch below)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            rs_s[j] += __shfl_xor_sync(0xffffffffu, rs_s[j], o);
+            rs_q[j] += __shfl_xor_sync(0xffffffffu, rs_q[j], o);
+          }
+        }
+        float* red = reinterpret_cast<float*>(staging);    // [8 warps][2][32]
+        if (lane == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            red[((warp - 2) * 2 + 0) * 32 + j] = rs_s[j];
+            red[((warp - 2) * 2 + 1) * 32 + j] = rs_q[j];
+          }
+        }
+        named_bar_sync(1, kEpiThreads);
+        const int et = threadIdx.x - 64;
+        if (et < 64) {                                      // channel et: column half et / 32, warps 4*half .. 4*half+3
+          const int hf = et >> 5, j = et & 31;
+          float sv = 0.f, qv = 0.f;
+          for (int wq = 0; wq < 4; ++wq) {
+            sv += red[((hf * 4 + wq) * 2 + 0) * 32 + j];
+            qv += red[((hf * 4 + wq) * 2 + 1) * 32 + j];
+          }
+          const int col = n_tile * 64 + et;
+          if (col < p.n_total) {
+            p.partials[((size_t)prow * 2 + 0) * p.n_total + col] = sv;
+            p.partials[((size_t)prow * 2 + 1) * p.n_total + col] = qv;
+          }
+        }
+      }
+      if (lane == 0) tma_store_wait_all<0>();
+    } else {
     // The epilogue is instruction-issue bound for the narrow (N = 64) layers, so everything that does
     // not depend on the tile is hoisted: per-thread staging addresses, the statistics addresses, and
     // the tile-coordinate divisions (only the one thread that issues the TMA store needs them unless
@@ -732,6 +854,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
       }
     }
     if (et == 0) tma_store_wait_all<0>();
+    }   // shared epilogue
   }
   tc_fence_before();
   __syncthreads();
@@ -1034,8 +1157,8 @@ static int pick_block_n(int n_total, int ocb) {
 }
 
 template <int BK, bool BMN, bool STRIP = false>
-static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const TapGemmParams& p,
-                      int grid, size_t smem, cudaStream_t st) {
+static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mo2,
+                      const TapGemmParams& p, int grid, size_t smem, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(tap_gemm_kernel<BK, BMN, STRIP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1044,7 +1167,7 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
     attr_done = true;
   }
   if (p.cluster == 1) {
-    return (int)launch_k(tap_gemm_kernel<BK, BMN, STRIP>, grid, kTapThreads, smem, st, ma, mb, mo, p);
+    return (int)launch_k(tap_gemm_kernel<BK, BMN, STRIP>, grid, kTapThreads, smem, st, ma, mb, mo, mo2, p);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
@@ -1058,7 +1181,7 @@ static int launch_tap(const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, tap_gemm_kernel<BK, BMN, STRIP>, ma, mb, mo, p);
+  return (int)cudaLaunchKernelEx(&cfg, tap_gemm_kernel<BK, BMN, STRIP>, ma, mb, mo, mo2, p);
 }
 
 static int cluster_env() {             // B200SEG_CLUSTER=1 enables CTA-pair weight multicast (off by default)
@@ -1067,9 +1190,9 @@ static int cluster_env() {             // B200SEG_CLUSTER=1 enables CTA-pair wei
   return v;
 }
 
-static int rows4_env() {               // four-row N-merged units (N = 64, resident bank): 0 off, 1 dgrad only (default), 2 also fprop
+static int rows4_env() {               // four-row N-merged units (N = 64, resident bank): 0 off, 1 dgrad only, 2 also fprop (default)
   static int v = -1;
-  if (v < 0) { const char* e = getenv("B200SEG_ROWS4"); v = (e == nullptr) ? 1 : (e[0] == '0' ? 0 : (e[0] == '2' ? 2 : 1)); }
+  if (v < 0) { const char* e = getenv("B200SEG_ROWS4"); v = (e == nullptr) ? 2 : (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2)); }
   return v;
 }
 
@@ -1152,9 +1275,9 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     if (p.rows2) p.staging_bufs = fits(2, 8, 6) ? 2 : 1;
     // four-row units with the vertical taps merged along N (resident bank, N = 64, one K chunk): the
     // bank's tiles must be exactly one 64-row block each so that stacked filter rows are contiguous.
-    // Measured (profiles/variants_in_situ.txt): dgrad 64->64 0.385 -> 0.326 ms; fprop unchanged (its
-    // epilogue with the BN statistics is the bound, not the MMAs), so fprop keeps the simpler units
-    // unless B200SEG_ROWS4=2.
+    // An M = 128, N = 64 UMMA occupies the tensor pipe as long as an N = 128 one (64 cycles, measured:
+    // profiles/ncu_mma_issue.txt), so merging is worth up to 2x on the MMA side.  With the warp-private
+    // epilogue it pays for fprop as well (64 -> 64 fprop 0.351 -> 0.241 ms, stem 0.271 -> 0.154 ms).
     p.rows4 = (p.b_resident && (rows4_env() == 2 || (rows4_env() == 1 && mode == 1)) && (H % 4 == 0) &&
                p.block_n == 64 && p.n_total == 64 &&
                p.kc_per_tap == 1 && p.stage_bytes == 64u * BK * 2u && fits(1, 6, 0)) ? 1 : 0;
@@ -1172,6 +1295,12 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
       if (p.rows2) xs -= xs % 4;                            // a K chunk's four strips never straddle the ring end
       p.xslots = xs;
     }
+  }
+  {
+    static int ep_env = -1;
+    if (ep_env < 0) { const char* e = getenv("B200SEG_EPI_PRIVATE"); ep_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    p.epi_private = (strip && ep_env && p.block_n == 64 && p.n_total == 64 && p.ocb == 64 && p.staging_bufs == 2 &&
+                     p.staging_bytes >= 16384 && kClusterSize == 1) ? 1 : 0;
   }
   if (!strip) {
     g = geom_for(N, H, W, 128);
@@ -1244,21 +1373,27 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     int box[5] = {p.ocb, 1, TW, 1, TH * g.tn};
     if (!make_map(&mo, out, 5, dims, str, box, p.ocb * 2)) return (int)cudaErrorInvalidValue;
   }
+  CUtensorMap mo2 = mo;
+  if (p.epi_private) {   // one 32-pixel x 32-channel slab per warp, plain (unswizzled) 64-byte rows
+    long long dims[4] = {n_total, W, H, N}, str[4] = {1, ld_o, ld_o * W, ld_o * W * H};
+    int box[4] = {32, 32, 1, 1};
+    if (!make_map(&mo2, out, 4, dims, str, box, 0)) return (int)cudaErrorInvalidValue;
+  }
   const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.xslots * p.xslot_bytes +
                       (size_t)p.staging_bufs * p.staging_bytes + 1024;
   if (strip) {
-    if (BK == 16) return launch_tap<16, false, true>(ma, mb, mo, p, grid, smem, st);
-    if (bmn) return launch_tap<64, true, true>(ma, mb, mo, p, grid, smem, st);
-    return launch_tap<64, false, true>(ma, mb, mo, p, grid, smem, st);
+    if (BK == 16) return launch_tap<16, false, true>(ma, mb, mo, mo2, p, grid, smem, st);
+    if (bmn) return launch_tap<64, true, true>(ma, mb, mo, mo2, p, grid, smem, st);
+    return launch_tap<64, false, true>(ma, mb, mo, mo2, p, grid, smem, st);
   }
   if (bmn) {
-    if (BK == 64) return launch_tap<64, true>(ma, mb, mo, p, grid, smem, st);
-    if (BK == 32) return launch_tap<32, true>(ma, mb, mo, p, grid, smem, st);
-    return launch_tap<16, true>(ma, mb, mo, p, grid, smem, st);
+    if (BK == 64) return launch_tap<64, true>(ma, mb, mo, mo2, p, grid, smem, st);
+    if (BK == 32) return launch_tap<32, true>(ma, mb, mo, mo2, p, grid, smem, st);
+    return launch_tap<16, true>(ma, mb, mo, mo2, p, grid, smem, st);
   }
-  if (BK == 64) return launch_tap<64, false>(ma, mb, mo, p, grid, smem, st);
-  if (BK == 32) return launch_tap<32, false>(ma, mb, mo, p, grid, smem, st);
-  return launch_tap<16, false>(ma, mb, mo, p, grid, smem, st);
+  if (BK == 64) return launch_tap<64, false>(ma, mb, mo, mo2, p, grid, smem, st);
+  if (BK == 32) return launch_tap<32, false>(ma, mb, mo, mo2, p, grid, smem, st);
+  return launch_tap<16, false>(ma, mb, mo, mo2, p, grid, smem, st);
 }
 
 }  // namespace b200

@@ -24,6 +24,7 @@ inline EncodeTiledFn encode_fn() {
 }
 
 inline CUtensorMapSwizzle swizzle_for_bytes(int inner_bytes) {
+  if (inner_bytes <= 0) return CU_TENSOR_MAP_SWIZZLE_NONE;       // plain rows (warp-private store slabs)
   if (inner_bytes >= 128) return CU_TENSOR_MAP_SWIZZLE_128B;
   if (inner_bytes >= 64) return CU_TENSOR_MAP_SWIZZLE_64B;
   return CU_TENSOR_MAP_SWIZZLE_32B;
