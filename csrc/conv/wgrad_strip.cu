@@ -311,10 +311,19 @@ static int launch_strip(const CUtensorMap& mx, const CUtensorMap& mdy, const Wgr
   return (int)launch_k(wgrad_strip_kernel<BN>, grid, kWsThreads, smem, st, mx, mdy, p);
 }
 
+extern "C" int b200conv_wgrad_pair(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
+                                   int N, int H, int W, int Cin, int Cout, cudaStream_t st);
+
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
                                     int N, int H, int W, int Cin, int Cout, cudaStream_t st) {
   if (!b200conv_wgrad_strip_supported(N, H, W, Cin, Cout)) return (int)cudaErrorInvalidValue;
   const int bn = strip_bn(W, Cin, Cout);
+  // 64-column tiles: the row-pair kernel (wgrad_pair.cu) issues N = 192 instructions where this one
+  // issues N = 64 ones, which hold the tensor pipe just as long as N = 128.  B200SEG_WGRAD_PAIR=0 keeps
+  // the old kernel (A/B runs).
+  static int pair_env = -1;
+  if (pair_env < 0) { const char* e = getenv("B200SEG_WGRAD_PAIR"); pair_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  if (bn == 64 && pair_env) return b200conv_wgrad_pair(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
   WgradStripParams p{};
   p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
   p.chunks = (Cin + 63) / 64;

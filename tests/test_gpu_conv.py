@@ -38,9 +38,11 @@ def _mk(N, H, W, Cin, Cout, seed=0):
     return x, w, b
 
 
-def test_fprop_four_row_units_forced(monkeypatch):
-    """The N-merged four-row units are the default for dgrad only; fprop takes them with B200SEG_ROWS4=2,
-    which has to be set before the library reads it, hence a subprocess."""
+@pytest.mark.parametrize("env", [{"B200SEG_ROWS4": "0"}, {"B200SEG_EPI_PRIVATE": "0"}, {"B200SEG_WGRAD_PAIR": "0"}])
+def test_fprop_alternative_paths(env):
+    """The defaults are four-row N-merged units, the warp-private epilogue and the row-pair wgrad; the paths
+    they replaced stay selectable (A/B runs) and must stay correct.  The switches are read once per process,
+    hence a subprocess."""
     import subprocess
     import sys
     code = (
@@ -54,9 +56,12 @@ def test_fprop_four_row_units_forced(monkeypatch):
         "    yr,_=ref.conv3x3_fwd(x.float(),w.float(),b,want_stats=False)\n"
         "    torch.testing.assert_close(y.float(),yr,rtol=2e-2,atol=2e-2)\n"
         "    torch.testing.assert_close(part.sum(0)[0],y.float().sum((0,1,2)),rtol=2e-3,atol=0.5)\n"
+        "    dy=(torch.randn(N,H,W,Co,device='cuda')*0.1).bfloat16(); dw=torch.zeros(Co,3,3,Ci,device='cuda'); dr=torch.zeros_like(dw)\n"
+        "    Fn.conv3x3_wgrad(x,dy,dw,impl='tcgen05'); ref.conv3x3_wgrad(x.float(),dy.float(),dr)\n"
+        "    assert (dw-dr).abs().max().item() <= 1e-2*dr.abs().max().item()+1e-3\n"
         "print('ok')\n")
     import os
-    env = dict(os.environ, B200SEG_ROWS4="2")
+    env = dict(os.environ, **env)
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
 
@@ -152,3 +157,73 @@ def test_convT2x2_bwd(N, h, w, C):
     torch.testing.assert_close(dbias, db_ref, rtol=1e-3, atol=1e-2)
     scale = (dw_ref - 1).abs().max().item()
     assert (dw_param - dw_ref).abs().max().item() <= 1e-2 * scale + 1e-3
+
+
+# ---- the shapes that bench.py times (headline config: U-Net b=64, batch 16, 512x512) ----------------------
+# Several waves of tiles per SM, double-buffered accumulators wrapping many times, full-size rings.
+BENCH_SHAPES = [  # N, H, W, Cin, Cout
+    (16, 512, 512, 64, 64),      # L0.c1 / L0.dec1: resident bank, four-row units, warp-private epilogue
+    (16, 512, 512, 192, 64),     # L0.dec0: streamed weights, two-row units
+    (16, 512, 512, 16, 64),      # stem
+    (16, 256, 256, 384, 128),    # L1.dec0
+    (16, 32, 32, 1024, 512),     # L4.dec0: box mode, split-K wgrad in CTA pairs
+    (16, 16, 16, 512, 512),      # L5
+]
+
+
+def _close_big(got, want, rtol, atol):
+    """assert_close without materialising several copies of a multi-GB tensor."""
+    err = (got.float() - want).abs_()
+    tol = want.abs().mul_(rtol).add_(atol)
+    bad = (err > tol).sum().item()
+    assert bad == 0, f"{bad} elements out of tolerance, max abs err {err.max().item():.4g}"
+
+
+@pytest.mark.parametrize("shape", BENCH_SHAPES)
+def test_bench_shapes_fprop_dgrad_wgrad(shape):
+    N, H, W, Cin, Cout = shape
+    x, w, _ = _mk(*shape, seed=3)
+    xn = x.float().permute(0, 3, 1, 2)
+    wn = w.float().permute(0, 3, 1, 2)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False                      # the oracle is plain fp32
+    try:
+        # fprop + BN statistics
+        y = torch.empty(N, H, W, Cout, dtype=torch.bfloat16, device=DEV)
+        part = Fn.conv3x3_fwd(x, w, None, y, want_stats=True, impl="tcgen05")
+        y_ref = F.conv2d(xn, wn, None, padding=1).permute(0, 2, 3, 1)
+        _close_big(y, y_ref, 2e-2, 2e-2)
+        want = torch.stack([y_ref.sum((0, 1, 2)), (y_ref ** 2).sum((0, 1, 2))])
+        torch.testing.assert_close(part.sum(0), want, rtol=3e-3, atol=0.03 * (N * H * W) ** 0.5)
+        del y_ref
+        dy = (torch.randn(N, H, W, Cout, device=DEV) * 0.1).to(torch.bfloat16)
+        dyn = dy.float().permute(0, 3, 1, 2)
+        # wgrad (accumulating)
+        dw = torch.ones(Cout, 3, 3, Cin, device=DEV)
+        Fn.conv3x3_wgrad(x, dy, dw, impl="tcgen05")
+        dw_ref = torch.nn.grad.conv2d_weight(xn, wn.shape, dyn, padding=1).permute(0, 2, 3, 1)
+        scale = dw_ref.abs().max().item()
+        assert (dw - 1 - dw_ref).abs().max().item() <= 1e-2 * scale + 1e-3
+        # dgrad
+        if Cin != 16:
+            dx = torch.empty(N, H, W, Cin, dtype=torch.bfloat16, device=DEV)
+            Fn.conv3x3_dgrad(dy, w, dx, impl="tcgen05")
+            dx_ref = torch.nn.grad.conv2d_input(xn.shape, wn, dyn, padding=1).permute(0, 2, 3, 1)
+            _close_big(dx, dx_ref, 2e-2, 3e-2)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+
+
+def test_bench_shape_convT():
+    N, h, w, C = 16, 256, 256, 128                                # up_conv1.up_sample of the headline config
+    torch.manual_seed(9)
+    x = torch.randn(N, h, w, C, device=DEV).to(torch.bfloat16)
+    wp = torch.randn(C, C, 2, 2, device=DEV) * 0.05
+    w_lp = wp.permute(2, 3, 1, 0).contiguous().view(4 * C, C).to(torch.bfloat16)
+    bias = torch.randn(C, device=DEV)
+    cat = torch.zeros(N, 2 * h, 2 * w, C + 64, dtype=torch.bfloat16, device=DEV)
+    Fn.convT2x2_fwd(x, wp, w_lp, bias, cat[..., :C], impl="tcgen05")
+    want = F.conv_transpose2d(x.float().permute(0, 3, 1, 2), w_lp.float().view(2, 2, C, C).permute(3, 2, 0, 1),
+                              bias, stride=2).permute(0, 2, 3, 1)
+    _close_big(cat[..., :C], want, 2e-2, 2e-2)
+    assert (cat[..., C:] == 0).all()
