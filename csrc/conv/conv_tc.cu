@@ -1549,6 +1549,9 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   return (int)launch_k(wgrad_kernel<1>, base_items * ks, kConvThreads, smem, st, mx, mdy, p);
 }
 
+extern "C" int b200conv_wgrad_pair_supported(int N, int H, int W, int Cin, int Cout);
+extern "C" int b200conv_wgrad_pair(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
+                                   int N, int H, int W, int Cin, int Cout, cudaStream_t st);
 extern "C" int b200conv_wgrad_strip_supported(int N, int H, int W, int Cin, int Cout);
 extern "C" int b200conv_wgrad_strip_preferred(int N, int H, int W, int Cin, int Cout);
 extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw,
@@ -1570,6 +1573,15 @@ extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, lon
     const char* e = getenv("B200SEG_WGRAD_KERNEL");
     force = (e == nullptr) ? 0 : (e[0] == 's' && e[1] == 'p' ? 1 : 2);
   }
+  static int pair_all = -1;            // B200SEG_WGRAD_PAIR=2: row-pair kernel for every layer it supports (A/B runs)
+  if (pair_all < 0) { const char* e = getenv("B200SEG_WGRAD_PAIR"); pair_all = (e != nullptr && e[0] == '2') ? 1 : 0; }
+  static int pair_off = -1;
+  if (pair_off < 0) { const char* e = getenv("B200SEG_WGRAD_PAIR"); pair_off = (e != nullptr && e[0] == '0') ? 1 : 0; }
+  // Measured per layer (profiles/conv_layers_b64_n16_512.txt): the row-pair kernel beats the 128-column strip
+  // kernel + its separate tap-(2,2) pass and the split-K kernel wherever rows are >= 64 pixels wide, except
+  // for the widest inputs (Cin > 512), where re-reading x once per 64-channel output tile costs more.
+  if (force == 0 && !pair_off && b200conv_wgrad_pair_supported(N, H, W, Cin, Cout) && (pair_all || Cin <= 512))
+    return b200conv_wgrad_pair(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
   const bool strip_ok = (force == 2) ? b200conv_wgrad_strip_supported(N, H, W, Cin, Cout) != 0
                                      : b200conv_wgrad_strip_preferred(N, H, W, Cin, Cout) != 0;
   if (strip_ok && force != 1) return b200conv_wgrad_strip(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
