@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--out", default="")
     ap.add_argument("--comm", default="auto", help="under torchrun: native | fused | torch")
+    ap.add_argument("--graph", action="store_true", help="profile CUDA-graph replays (steady state, as bench.py runs)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -35,7 +36,7 @@ def main():
         from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
         cfg = TrainConfig(base_channels=a.base_channels, tile=a.tile, batch_size=a.batch, sync_every=1, codec="fp32",
                           world_size=world, rank=rank, comm=a.comm, train_tiles=a.batch, holdout_tiles=0,
-                          sample_images=0, cuda_graph=False,
+                          sample_images=0, cuda_graph=a.graph,
                           out_dir=os.path.join(ROOT, "gpurun_out", "prof_run"), device="cuda")
         if world > 1:
             cfg = cfg.apply_env()
@@ -64,6 +65,13 @@ def main():
     for _ in range(3):
         step()
     torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    step_ms = e0.elapsed_time(e1) / 10
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         for _ in range(a.steps):
             step()
@@ -75,7 +83,8 @@ def main():
             rows.append((t / a.steps / 1e3, ev.count / a.steps, ev.key))
     rows.sort(reverse=True)
     total = sum(r[0] for r in rows)
-    lines = [f"total kernel ms/step {total:.3f}  impl={a.impl} conv={a.conv}"]
+    lines = [f"total kernel ms/step {total:.3f}  impl={a.impl} conv={a.conv}  graph={getattr(a, 'graph', False)}  "
+             f"step (CUDA events, no profiler) {step_ms:.3f} ms -> not in kernels {step_ms - total:.3f} ms"]
     for ms, cnt, name in rows[:40]:
         lines.append(f"{ms:9.3f} ms {100 * ms / total:5.1f}%  x{cnt:6.1f}  {name[:110]}")
     text = "\n".join(lines)

@@ -318,6 +318,8 @@ int64_t overlap_max_buckets() { return b200seg_overlap_max_buckets(); }
 int64_t overlap_flag_index(int64_t bucket, int64_t rank) { return b200seg_overlap_flag_index((int)bucket, (int)rank); }
 int64_t overlap_abort_index() { return b200seg_overlap_abort_index(); }
 
+void set_comm_timeout(double seconds) { b200seg_set_comm_timeout(seconds); }
+int64_t allreduce_abort_word() { return b200seg_allreduce_abort_word(); }
 int64_t allreduce_signal_bytes() { return b200seg_allreduce_signal_bytes(); }
 int64_t allreduce_max_blocks() { return b200seg_allreduce_max_blocks(); }
 
@@ -380,6 +382,8 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("overlap_max_buckets() -> int", &overlap_max_buckets);
   m.def("overlap_flag_index(int bucket, int rank) -> int", &overlap_flag_index);
   m.def("overlap_abort_index() -> int", &overlap_abort_index);
+  m.def("set_comm_timeout(float seconds) -> ()", &set_comm_timeout);
+  m.def("allreduce_abort_word() -> int", &allreduce_abort_word);
   m.def("allreduce_signal_bytes() -> int", &allreduce_signal_bytes);
   m.def("allreduce_max_blocks() -> int", &allreduce_max_blocks);
   m.def("conv3x3_fwd(Tensor x, Tensor w, Tensor? bias, Tensor(a!) y, bool want_stats) -> Tensor", &conv3x3_fwd);

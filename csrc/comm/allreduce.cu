@@ -16,8 +16,9 @@
 //     reduces locally into a private output.
 //
 // Cross-GPU ordering uses per-CTA flags in a symmetric signal pad: st.release.sys to the peer,
-// ld.acquire.sys spin (bounded, then trap) on the local pad, with a monotonically increasing
-// epoch so pads never need clearing.
+// ld.acquire.sys spin on the local pad (bounded by %globaltimer; on expiry an abort word is raised in
+// every rank's pad and the kernels return), with a monotonically increasing epoch so pads never need
+// clearing.
 #include "../common.cuh"
 #include "b200seg.h"
 #include <cuda_fp16.h>
@@ -44,20 +45,48 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   return v;
 }
 
-// Every CTA b of every rank meets CTA b of all other ranks.
-__device__ __forceinline__ void cross_gpu_barrier(const PeerPtrs& pp, int rank, int world, uint32_t epoch) {
+// Word (in uint32 units) of the abort flag inside every rank's signal pad: behind the per-CTA flags and the
+// multiplier slot.  Non-zero = some rank gave up waiting (value = 0x80000000 | rank); sticky.
+constexpr int kAbortWord = 256 * kMaxRanks + 8;
+static unsigned long long g_comm_timeout_ns = 600ull * 1000000000ull;
+
+__device__ __forceinline__ unsigned long long ar_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Every CTA b of every rank meets CTA b of all other ranks.  The wait is bounded by %globaltimer: when a peer
+// does not arrive within `timeout_ns` (it stalled or died -- the reference would sit in recv forever, R:98)
+// the waiting thread raises the abort word in EVERY rank's pad and the kernel returns without touching the
+// gradients; the host turns the word into PeerLost (parallel/symm.py check_abort).  Returns false then.
+__device__ __forceinline__ bool cross_gpu_barrier(const PeerPtrs& pp, int rank, int world, uint32_t epoch,
+                                                  unsigned long long timeout_ns) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
   __syncthreads();
   if (threadIdx.x < world) {
     const int peer = threadIdx.x;
     __threadfence_system();
     st_release_sys(pp.signal[peer] + (size_t)blockIdx.x * kMaxRanks + rank, epoch);
     const uint32_t* mine = pp.signal[rank] + (size_t)blockIdx.x * kMaxRanks + peer;
-    long long spins = 0;
-    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
-      if (++spins > (1ll << 31)) { asm volatile("trap;"); }
+    const uint32_t* my_abort = pp.signal[rank] + kAbortWord;
+    unsigned long long t0 = 0;
+    for (unsigned int spin = 0; (int)(ld_acquire_sys(mine) - epoch) < 0; ++spin) {
+      if ((spin & 255u) == 255u) {
+        if (ld_acquire_sys(my_abort) != 0u) { s_ok = 0; break; }
+        const unsigned long long now = ar_now();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > timeout_ns) {
+          for (int r = 0; r < world; ++r) st_release_sys(pp.signal[r] + kAbortWord, 0x80000000u | (uint32_t)rank);
+          s_ok = 0;
+          break;
+        }
+      }
     }
   }
   __syncthreads();
+  return s_ok != 0;
 }
 
 template <typename T> struct Wire;
@@ -107,9 +136,9 @@ template <> struct Wire<__nv_fp8_e4m3> {
 template <typename T, bool ONESHOT>
 __global__ void __launch_bounds__(kArThreads)
 allreduce_kernel(PeerPtrs pp, int rank, int world, size_t n_vec, float post_scale, uint32_t epoch,
-                 float* __restrict__ oneshot_out) {
+                 float* __restrict__ oneshot_out, unsigned long long timeout_ns) {
   constexpr int V = Wire<T>::kVec;
-  cross_gpu_barrier(pp, rank, world, epoch);           // every rank's wire buffer is complete
+  if (!cross_gpu_barrier(pp, rank, world, epoch, timeout_ns)) return;   // every rank's wire buffer is complete
   float mult[kMaxRanks];
 #pragma unroll
   for (int r = 0; r < kMaxRanks; ++r)
@@ -159,7 +188,9 @@ allreduce_kernel(PeerPtrs pp, int rank, int world, size_t n_vec, float post_scal
       }
     }
   }
-  if (!ONESHOT) cross_gpu_barrier(pp, rank, world, epoch + 1);   // all slices have landed everywhere
+  // two-shot: all slices have landed everywhere.  one-shot: nobody may overwrite its wire buffer (with fp32 it
+  // IS the gradient buffer, which the caller copies the result into next) while a slower peer still reads it.
+  cross_gpu_barrier(pp, rank, world, epoch + 1, timeout_ns);
 }
 
 template <typename T>
@@ -167,9 +198,11 @@ static int launch_ar(const PeerPtrs& pp, int rank, int world, size_t n_elems, fl
                      uint32_t epoch, float* oneshot_out, int blocks, cudaStream_t st) {
   const size_t n_vec = n_elems / Wire<T>::kVec;
   if (oneshot_out != nullptr)
-    allreduce_kernel<T, true><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, oneshot_out);
+    allreduce_kernel<T, true><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, oneshot_out,
+                                                             g_comm_timeout_ns);
   else
-    allreduce_kernel<T, false><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, nullptr);
+    allreduce_kernel<T, false><<<blocks, kArThreads, 0, st>>>(pp, rank, world, n_vec, post_scale, epoch, nullptr,
+                                                              g_comm_timeout_ns);
   return (int)cudaGetLastError();
 }
 
@@ -185,29 +218,40 @@ namespace b200 {
 // GPU moves ~S/W bytes in and S/W out instead of (W-1)/W * S each way.
 __global__ void __launch_bounds__(kArThreads)
 allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, size_t n_vec, float post_scale,
-                      uint32_t epoch) {
-  cross_gpu_barrier(pp, rank, world, epoch);
+                      uint32_t epoch, unsigned long long timeout_ns) {
+  if (!cross_gpu_barrier(pp, rank, world, epoch, timeout_ns)) return;
   const size_t per = (n_vec + world - 1) / world;
   const size_t v0 = (size_t)rank * per;
   const size_t v1 = v0 + per < n_vec ? v0 + per : n_vec;
-  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1;
-       i += (size_t)gridDim.x * blockDim.x) {
-    float4 v;
-    float* addr = mc + i * 4;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "l"(addr)
-                 : "memory");
-    v.x *= post_scale; v.y *= post_scale; v.z *= post_scale; v.w *= post_scale;
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y),
-                 "f"(v.z), "f"(v.w)
-                 : "memory");
+  const size_t nthr = (size_t)gridDim.x * blockDim.x;
+  // four independent 16-byte switch reductions in flight per thread before the first store
+  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += 4 * nthr) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t j = i + (size_t)u * nthr;
+      if (j < v1)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w)
+                     : "l"(mc + j * 4)
+                     : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t j = i + (size_t)u * nthr;
+      if (j < v1) {
+        v[u].x *= post_scale; v[u].y *= post_scale; v[u].z *= post_scale; v[u].w *= post_scale;
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + j * 4), "f"(v[u].x),
+                     "f"(v[u].y), "f"(v[u].z), "f"(v[u].w)
+                     : "memory");
+      }
+    }
   }
-  cross_gpu_barrier(pp, rank, world, epoch + 1);
+  cross_gpu_barrier(pp, rank, world, epoch + 1, timeout_ns);
 }
 
-__global__ void barrier_kernel(PeerPtrs pp, int rank, int world, uint32_t epoch) {
-  cross_gpu_barrier(pp, rank, world, epoch);
+__global__ void barrier_kernel(PeerPtrs pp, int rank, int world, uint32_t epoch, unsigned long long timeout_ns) {
+  cross_gpu_barrier(pp, rank, world, epoch, timeout_ns);
 }
 
 // Registered multicast alias of the gradient buffer (fused wgrad -> all-reduce, see grad_red_add).
@@ -234,7 +278,7 @@ extern "C" int b200seg_barrier(unsigned int* const* signal_ptrs, int rank, int w
   if (world < 2 || world > kMaxRanks) return (int)cudaErrorInvalidValue;
   PeerPtrs pp{};
   for (int r = 0; r < world; ++r) pp.signal[r] = signal_ptrs[r];
-  barrier_kernel<<<1, 32, 0, st>>>(pp, rank, world, epoch);
+  barrier_kernel<<<1, 32, 0, st>>>(pp, rank, world, epoch, g_comm_timeout_ns);
   return (int)cudaGetLastError();
 }
 
@@ -257,6 +301,12 @@ extern "C" long long b200seg_grad_multicast_delta(const void* p) {
   const char* c = static_cast<const char*>(p);
   return (g_mc_local != nullptr && c >= g_mc_local && c < g_mc_local + g_mc_bytes) ? g_mc_delta : 0;
 }
+
+// Bound (seconds) on every device-side wait for a peer; process-wide, read at launch time.
+extern "C" void b200seg_set_comm_timeout(double seconds) {
+  g_comm_timeout_ns = (unsigned long long)((seconds > 0 ? seconds : 600.0) * 1e9);
+}
+extern "C" int b200seg_allreduce_abort_word() { return kAbortWord; }
 
 extern "C" int b200seg_allreduce_max_blocks() { return 256; }   // all co-resident: 4 x 512 threads per SM
 extern "C" long long b200seg_allreduce_signal_bytes() {
@@ -300,6 +350,6 @@ extern "C" int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* m
   PeerPtrs pp{};
   for (int r = 0; r < world; ++r) pp.signal[r] = signal_ptrs[r];
   allreduce_nvls_kernel<<<blocks, kArThreads, 0, st>>>(pp, multicast_ptr, rank, world, (size_t)n_elems / 4, post_scale,
-                                                      epoch);
+                                                      epoch, g_comm_timeout_ns);
   return (int)cudaGetLastError();
 }

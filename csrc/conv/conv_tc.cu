@@ -889,6 +889,7 @@ struct WgradParams {
   long long mc_delta;                       // != 0: add through the multicast alias (fused all-reduce)
   int quads;                                // convT: output quadrants per CTA (4 = all share one x tile), else 1
   const GradArm* arm;                       // != NULL: this launch completes a gradient bucket (all-reduce trigger)
+  int vec_red;                              // 16-byte vector reductions (needs Cin % 4 == 0 and whole quads of rows)
 };
 
 // CSZ = 2: CTA pairs (two adjacent M tiles of the same N tile and K slice) share every dy tile: each CTA
@@ -1081,17 +1082,28 @@ wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
             for (int j = 0; j < 16; ++j) { r[j] = r16[j]; r[j + 16] = 0u; }
           }
           tmem_ld_wait();
-          if (p.mc_delta != 0) {                              // fused all-reduce: 16-byte multicast reductions
+          if (p.vec_red) {
+            // 16-byte reductions: after the quad transpose a lane holds four CONSECUTIVE input channels of
+            // one output channel, i.e. 16 contiguous bytes of dW -> red.global.add.v4.f32 (a quarter of the
+            // reduction instructions; the split-K epilogue was atomics-bound on the deep layers), or
+            // multimem.red through the multicast alias in fused mode.
             quad_transpose32(r, lane);
             float* qbase = base - (lane & 3);
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
               const int cj = c0 + 4 * g + (lane & 3);
               const int co = co_base + cj;
-              if (row_ok && cj < p.block_n && co < co_lim)
-                grad_red_add4_mc(qbase + (size_t)co * co_stride, __uint_as_float(r[4 * g]),
-                                 __uint_as_float(r[4 * g + 1]), __uint_as_float(r[4 * g + 2]),
-                                 __uint_as_float(r[4 * g + 3]), p.mc_delta);
+              if (row_ok && cj < p.block_n && co < co_lim) {
+                float* dst = qbase + (size_t)co * co_stride;
+                if (p.mc_delta != 0)
+                  grad_red_add4_mc(dst, __uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1]),
+                                   __uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3]), p.mc_delta);
+                else
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(__uint_as_float(r[4 * g])),
+                               "f"(__uint_as_float(r[4 * g + 1])), "f"(__uint_as_float(r[4 * g + 2])),
+                               "f"(__uint_as_float(r[4 * g + 3]))
+                               : "memory");
+              }
             }
           } else if (row_ok) {
 #pragma unroll
@@ -1486,7 +1498,16 @@ static int run_wgrad(int convt, const void* x, long long ld_x, const void* dy, l
   if (stages > kMaxStages) stages = kMaxStages;
   p.stages = stages;
   const int base_items = p.m_tiles * p.n_tiles;
-  int ks = (2 * kNumSMs) / base_items;
+  static int waves_env = -1, vec_env = -1;
+  if (waves_env < 0) { const char* e = getenv("B200SEG_WGRAD_WAVES"); waves_env = (e != nullptr && e[0] == '1') ? 1 : 2; }
+  if (vec_env < 0) { const char* e = getenv("B200SEG_WGRAD_VEC"); vec_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  // a quad of rows = four consecutive input channels of one 64-channel block: whole quads need Cin % 4 == 0
+  p.vec_red = (vec_env && Cin % 4 == 0) || b200seg_grad_multicast_delta(dw) != 0 ? 1 : 0;
+  // split-K factor: two waves of CTAs hide the prologue / epilogue of one behind the main loop of the other,
+  // but every extra slice adds a full set of partial sums to reduce; with few pixels (<= 256 tiles of 64) one
+  // wave is faster (L4.c0 0.085 -> 0.080 ms, L5 0.043 -> 0.031 ms; L3 and up prefer two).
+  const int waves = (waves_env == 1 || p.p_tiles <= 256) ? 1 : 2;
+  int ks = (waves * kNumSMs) / base_items;
   if (ks < 1) ks = 1;
   if (ks > p.p_tiles) ks = p.p_tiles;
   p.k_slices = ks;

@@ -493,6 +493,27 @@ static int head_fast_env() {           // B200SEG_HEAD_FAST=0 keeps the generic 
 
 using namespace b200;
 
+// The general kernels' dynamic shared memory limit is raised ONCE per device to the most the device allows
+// (not per call to the size of that call: two host threads could interleave so that one lowers the limit
+// just before the other launches with a larger request).
+#include <mutex>
+template <int KMAX>
+static cudaError_t head_ce_raise_smem_limit() {
+  static std::mutex mu;
+  static bool done[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
+  int optin = 0;
+  e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b200::head_ce_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
+  return e;
+}
+
 extern "C" long long b200seg_head_ce_workspace_bytes(int C, int K) {
   return (long long)(2 * kNumSMs) * (K * C + K + 2) * (long long)sizeof(float) + 256;
 }
@@ -532,13 +553,13 @@ extern "C" int b200seg_head_ce(const void* a, long long ld_a, const float* w, co
   }
   cudaError_t e;
   if (KMAX == 8) {
-    e = cudaFuncSetAttribute(head_ce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = head_ce_raise_smem_limit<8>();
     if (e != cudaSuccess) return (int)e;
     head_ce_kernel<8><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
                                                    grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc,
                                                    ws, counter, warps);
   } else {
-    e = cudaFuncSetAttribute(head_ce_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = head_ce_raise_smem_limit<16>();
     if (e != cudaSuccess) return (int)e;
     head_ce_kernel<16><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K,
                                                     grad_scale, (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc,
@@ -635,7 +656,7 @@ extern "C" int b200seg_head_ce_static(const void* a, long long ld_a, const float
   const int nred = K * C + K + 2;
   const size_t smem = sizeof(float) * ((size_t)K * C + 8 + ((nred + 3) & ~3) + (size_t)warps * 32 * 8) +
                       (size_t)warps * 2 * 32 * (C + 8) * 2;
-  e = cudaFuncSetAttribute(head_ce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = head_ce_raise_smem_limit<8>();
   if (e != cudaSuccess) return (int)e;
   head_ce_kernel<8><<<grid, threads, smem, st>>>((const __nv_bfloat16*)a, ld_a, w, bias, labels, P, C, K, grad_scale,
                                                  (__nv_bfloat16*)da, ld_da, dw, db, pred, loss_acc, partials,

@@ -10,8 +10,6 @@ from .trainer import Trainer
 
 def main(argv=None) -> int:
     cfg = parse_cli(argv)
-    if cfg.world_size == 1 and cfg.rank == 0:
-        pass
     trainer = Trainer(cfg)
     try:
         last = trainer.fit()

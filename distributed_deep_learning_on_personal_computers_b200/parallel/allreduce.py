@@ -41,8 +41,8 @@ from .dist import DistContext
 class GradientSynchronizer:
     def __init__(self, flat_grad: torch.Tensor, ctx: DistContext, codec: str = "fp32",
                  reduce: str = "mean", accumulate: str = "mean", backend: str = "auto",
-                 requantize_output: bool = False, star=None, bucket_mb: float = 25.0,
-                 fused_bulk_elems: int = 0):
+                 requantize_output: bool = False, star=None, fused_bulk_elems: int = 0,
+                 timeout_s: float = 600.0):
         self.flat = flat_grad
         self.ctx = ctx
         self.codec: Codec = get_codec(codec)
@@ -50,7 +50,6 @@ class GradientSynchronizer:
         self.accumulate = accumulate
         self.requantize_output = requantize_output
         self.star = star
-        self.bucket_elems = max(int(bucket_mb * (1 << 20)) // 4, 1)
         if backend == "auto":
             backend = "star" if star is not None else "torch"
             if star is None and flat_grad.is_cuda and ctx.world_size > 1:
@@ -68,7 +67,8 @@ class GradientSynchronizer:
         if backend == "native" and ctx.world_size > 1:
             from . import symm
             self.native = symm.SymmetricAllReduce(flat_grad, ctx, self.codec,
-                                                  fused_bulk_elems=fused_bulk_elems if self.fused else 0)
+                                                  fused_bulk_elems=fused_bulk_elems if self.fused else 0,
+                                                  timeout_s=timeout_s)
             self.flat = self.native.buffer          # gradients now live in symmetric memory
         self.timings: Dict[str, float] = {}
         self.bytes_on_wire = 0

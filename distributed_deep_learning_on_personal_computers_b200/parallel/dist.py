@@ -33,6 +33,7 @@ class DistContext:
     device: torch.device = torch.device("cpu")
     backend: str = "none"
     initialized_here: bool = False
+    star: object = None              # backend "star": the TCP endpoint (StarServer on rank 0, StarWorker elsewhere)
 
     @property
     def is_coordinator(self) -> bool:
@@ -40,12 +41,23 @@ class DistContext:
 
     def barrier(self) -> None:
         if self.world_size > 1:
-            if self.backend == "nccl":
+            if self.backend == "star":
+                # the reference has no barrier; its blocking recv is one (R:215-220).  Same thing, explicit.
+                if self.rank == 0:
+                    self.star.gather()
+                    self.star.broadcast({"barrier": 1})
+                else:
+                    self.star.send({"barrier": 1})
+                    self.star.recv()
+            elif self.backend == "nccl":
                 dist.barrier(device_ids=[self.device.index])
             else:
                 dist.barrier()
 
     def shutdown(self) -> None:
+        if self.star is not None:
+            self.star.close()
+            self.star = None
         if self.initialized_here and dist.is_initialized():
             dist.destroy_process_group()
             self.initialized_here = False
@@ -67,6 +79,11 @@ def init(cfg) -> DistContext:
     device = pick_device(cfg)
     if cfg.world_size <= 1:
         return DistContext(0, 1, cfg.local_rank, device, "none", False)
+    if cfg.comm == "star":
+        # The reference's own bootstrap: bare TCP sockets, rank 0 listens and accepts world-1 connections
+        # (R:173-206).  No torch.distributed process group exists on this path: rendezvous, the initial
+        # state broadcast, the gradient rounds and the barriers all go over the star.
+        return DistContext(cfg.rank, cfg.world_size, cfg.local_rank, device, "star", False, open_star(cfg))
     backend = cfg.backend
     if backend == "auto":
         backend = "nccl" if device.type == "cuda" else "gloo"
@@ -86,10 +103,36 @@ def init(cfg) -> DistContext:
                        dist.get_backend(), started)
 
 
+def open_star(cfg):
+    """Rank 0 listens on ``master_addr:master_port + 1`` and waits for every worker; workers connect with
+    retries (R:173-206, with the timeouts the reference lacks)."""
+    from . import star
+    kw = dict(compress=cfg.compress, level=cfg.compress_level, threads=cfg.compress_threads,
+              block=cfg.compress_block)
+    port = cfg.master_port + 1
+    if cfg.rank == 0:
+        srv = star.StarServer(cfg.master_addr, port, cfg.world_size - 1, cfg.timeout_s, **kw)
+        srv.accept_all()
+        return srv
+    return star.StarWorker(cfg.master_addr, port, cfg.rank, cfg.timeout_s, **kw)
+
+
 @torch.no_grad()
 def broadcast_model_state(model, ctx: DistContext, src: int = 0) -> None:
     """Make every replica start from rank ``src``'s parameters and BN buffers (R:560-565)."""
     if ctx.world_size <= 1:
+        return
+    if ctx.backend == "star":
+        # tensors, not pickled modules: rank 0 packs the flat parameter buffer and the BN buffers once
+        flat = model.flat
+        if ctx.rank == 0:
+            ctx.star.broadcast({"param": flat["param"].detach().cpu(),
+                                "buffers": [b.detach().cpu() for b in model.buffers()]})
+        else:
+            msg = ctx.star.recv()
+            flat["param"].copy_(msg["param"].to(flat["param"].device).view_as(flat["param"]))
+            for b, v in zip(model.buffers(), msg["buffers"]):
+                b.copy_(v.to(b.device).view_as(b))
         return
     flat = getattr(model, "_flat", None)
     if flat:
@@ -103,7 +146,7 @@ def broadcast_model_state(model, ctx: DistContext, src: int = 0) -> None:
 
 def all_reduce_max_time(ms: float, ctx: DistContext) -> float:
     """Max over ranks of a device-measured duration (multi-GPU numbers are max-over-ranks)."""
-    if ctx.world_size <= 1:
+    if ctx.world_size <= 1 or ctx.backend == "star":
         return ms
     t = torch.tensor([ms], dtype=torch.float64, device=ctx.device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)

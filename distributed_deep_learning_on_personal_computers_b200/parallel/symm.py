@@ -47,7 +47,7 @@ def available(ctx: DistContext) -> bool:
 
 class SymmetricAllReduce:
     def __init__(self, like_flat: torch.Tensor, ctx: DistContext, codec: Codec, group=None,
-                 algorithm: str = "auto", fused_bulk_elems: int = 0):
+                 algorithm: str = "auto", fused_bulk_elems: int = 0, timeout_s: float = 600.0):
         import torch.distributed._symmetric_memory as symm_mem
         from ..ops import loader
         if loader.library() is None:
@@ -62,6 +62,9 @@ class SymmetricAllReduce:
         self.buffer = self.buffer_full[:n]
         self.h_grad = symm_mem.rendezvous(self.buffer_full, self.group)
         ops = torch.ops.b200seg
+        self.timeout_s = float(timeout_s)
+        ops.set_comm_timeout(self.timeout_s)               # bounds every device-side wait for a peer
+        self.abort_word = int(ops.allreduce_abort_word())
         sig_words = ops.allreduce_signal_bytes() // 4 + 64
         self.signal = symm_mem.empty(sig_words, dtype=torch.int32, device=dev)
         self.signal.zero_()
@@ -175,15 +178,15 @@ class SymmetricAllReduce:
 
     def check_abort(self) -> None:
         """Raise ``PeerLost`` if a bounded wait on the device gave up (synchronizes the device)."""
+        torch.cuda.synchronize(self.signal.device)
+        word = int(self.signal[self.abort_word].item()) & 0xFFFFFFFF
         pad = getattr(self, "ovl_pad", None)
-        if pad is None:
-            return
-        torch.cuda.synchronize(pad.device)
-        word = int(pad[self.ovl_abort_index].item()) & 0xFFFFFFFF
+        if not word and pad is not None:
+            word = int(pad[self.ovl_abort_index].item()) & 0xFFFFFFFF
         if word:
             from .star import PeerLost
-            raise PeerLost(f"gradient exchange timed out on rank {word & 0xFFFF} after {self.ovl_timeout_s:.0f} s "
-                           "(a peer did not publish its bucket); the step's gradients are not reduced")
+            raise PeerLost(f"gradient exchange timed out on rank {word & 0xFFFF} after {self.timeout_s:.0f} s "
+                           "(a peer did not arrive); the step's gradients are not reduced")
 
     @property
     def multicast_supported(self) -> bool:

@@ -52,15 +52,13 @@ class Trainer:
         self.model.flatten_parameters(dev)
         pdist.broadcast_model_state(self.model, self.ctx)   # rank 0 -> all (R:560-565)
 
-        self.star = None
         comm = cfg.comm
-        if comm == "star" and cfg.world_size > 1:
-            self.star = self._open_star()
+        self.star = self.ctx.star if comm == "star" else None    # opened by the rendezvous (parallel/dist.py)
         self.sync = GradientSynchronizer(
             self.model.flat["grad"], self.ctx, codec=cfg.codec, reduce=cfg.reduce,
             accumulate=cfg.accumulate, backend=("auto" if comm == "auto" else comm),
-            requantize_output=cfg.requantize_output, star=self.star, bucket_mb=cfg.bucket_mb,
-            fused_bulk_elems=self.model.flat.get("bulk_elems", 0))
+            requantize_output=cfg.requantize_output, star=self.star,
+            fused_bulk_elems=self.model.flat.get("bulk_elems", 0), timeout_s=cfg.timeout_s)
         if self.sync.flat is not self.model.flat["grad"]:
             self._rebind_grad(self.sync.flat)
 
@@ -100,19 +98,6 @@ class Trainer:
             self.resume(cfg.resume)
 
     # -- plumbing ----------------------------------------------------------------------------------
-    def _open_star(self):
-        from .parallel import star
-        kw = dict(compress=self.cfg.compress, level=self.cfg.compress_level,
-                  threads=self.cfg.compress_threads, block=self.cfg.compress_block)
-        port = self.cfg.master_port + 1
-        if self.ctx.rank == 0:
-            srv = star.StarServer(self.cfg.master_addr, port, self.ctx.world_size - 1,
-                                  self.cfg.timeout_s, **kw)
-            srv.accept_all()
-            return _StarFacade(srv)
-        return _StarFacade(star.StarWorker(self.cfg.master_addr, port, self.ctx.rank,
-                                           self.cfg.timeout_s, **kw))
-
     def _rebind_grad(self, new_flat: torch.Tensor) -> None:
         """Point every ``.grad`` view (and the engine / optimizer) at ``new_flat``."""
         m = self.model
@@ -380,30 +365,6 @@ class Trainer:
             self.engine.refresh_lowp()
 
     def close(self) -> None:
-        if self.star is not None:
-            self.star.close()
         if getattr(self.sync, "native", None) is not None:
             self.sync.native.close()
         self.ctx.shutdown()
-
-
-class _StarFacade:
-    """Gives server and worker endpoints the one interface ``GradientSynchronizer`` uses."""
-
-    def __init__(self, endpoint):
-        self.ep = endpoint
-
-    def send(self, obj):
-        return self.ep.send(obj)
-
-    def recv(self):
-        return self.ep.recv()
-
-    def gather(self):
-        return self.ep.gather()
-
-    def broadcast(self, obj):
-        return self.ep.broadcast(obj)
-
-    def close(self):
-        self.ep.close()

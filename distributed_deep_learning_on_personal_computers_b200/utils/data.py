@@ -72,7 +72,10 @@ def load_directory(path: str, holdout: int = 30) -> Tuple[TileSet, TileSet]:
     if len(xs) != len(ys) or not xs:
         raise ValueError(f"{path}: {len(xs)} images vs {len(ys)} label maps")
     x = torch.from_numpy(np.stack(xs).astype(np.uint8))
-    y = torch.from_numpy(np.stack(ys).astype(np.uint8))
+    ys = np.stack(ys)
+    if ys.min() < 0 or ys.max() > 255:          # astype(uint8) would wrap such values silently
+        raise ValueError(f"label values must lie in [0, 255], found [{ys.min()}, {ys.max()}]")
+    y = torch.from_numpy(ys.astype(np.uint8))
     holdout = min(holdout, len(xs) - 1) if holdout else 0
     cut = len(xs) - holdout
     return TileSet(x[:cut], y[:cut]), TileSet(x[cut:], y[cut:])
@@ -216,6 +219,12 @@ class PinnedBatchLoader:
 def build_datasets(cfg) -> Tuple[TileSet, Optional[TileSet]]:
     if cfg.data_dir:
         train, hold = load_directory(cfg.data_dir, cfg.holdout_tiles)
+        # nn.CrossEntropyLoss (R:703) raises on a class index >= out_classes; the fused head kernel does not
+        # look (such a pixel would get a gradient with no one-hot term), so the check happens once, here.
+        for name, ts in (("train", train), ("hold-out", hold)):
+            if len(ts) and int(ts.labels.max()) >= cfg.out_classes:
+                raise ValueError(f"{name} labels contain class {int(ts.labels.max())} but out_classes = "
+                                 f"{cfg.out_classes}")
         return train, (hold if len(hold) else None)
     # train and hold-out share the class palette, so the hold-out measures generalisation
     train = synthetic_tiles(cfg.train_tiles, cfg.tile, cfg.out_classes, cfg.seed,

@@ -84,6 +84,11 @@ int b200seg_upsample2x_bwd(const void* g, long long ld_g, void* dx, long long ld
  * wire_kind: 0 fp32, 1 bf16, 2 fp16 (also q201), 3 int8 (q21, int8s), 4 fp8.  n_elems % 16 == 0.
  * oneshot_out == NULL: in-place two-shot into every rank's grad buffer; else one-shot into
  * oneshot_out.  Two epochs are consumed per call: pass epoch = 2 * call_index + 1. */
+/* Every device-side wait for a peer is bounded (default 600 s; the reference blocks forever in recv, R:98).
+ * On expiry the waiting rank stores 0x80000000 | rank into word b200seg_allreduce_abort_word() of EVERY
+ * rank's signal pad and the kernels return without reducing; the host polls that word. */
+void b200seg_set_comm_timeout(double seconds);
+int b200seg_allreduce_abort_word(void);
 int b200seg_allreduce_max_blocks(void);
 long long b200seg_allreduce_signal_bytes(void);
 int b200seg_write_mult(const float* scale, float levels, float* out, cudaStream_t st);

@@ -34,6 +34,9 @@ def _worker(rank, world, port, out_dir, overrides, result_q):
     if rank != 0:
         torch.manual_seed(1234 + rank)          # ranks start different; the broadcast must fix it
     tr = Trainer(cfg)
+    if cfg.comm == "star":                      # the TCP star bootstraps the job by itself (R:173-206)
+        import torch.distributed as dist
+        assert not dist.is_initialized(), "comm=star must not need a torch.distributed process group"
     first = None
     losses = []
     for _ in range(cfg.epochs):

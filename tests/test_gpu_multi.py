@@ -352,3 +352,56 @@ def test_stalled_peer_raises_peer_lost_and_leaves_a_checkpoint(tmp_path):
     import torch as _t
     state = _t.load(os.path.join(str(tmp_path), "abort.pt"), weights_only=True)
     assert "model" in state and "optimizer" in state
+
+
+def _oneshot_worker(rank, world, port, q):
+    """The latency-optimal one-shot path, many calls in a row with deliberately skewed ranks: a rank that runs
+    ahead must not overwrite its buffer while a slower peer still reads it (trailing barrier)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    from distributed_deep_learning_on_personal_computers_b200.parallel import symm, dist as pdist
+    from distributed_deep_learning_on_personal_computers_b200.parallel.codecs import get_codec
+    ctx = pdist.DistContext(rank, world, rank, torch.device("cuda", rank), "nccl", False)
+    n = 1 << 15
+    g = torch.Generator(device="cuda").manual_seed(5 + rank)
+    xs = [torch.randn(n, device="cuda", generator=g) for _ in range(4)]
+    ar = symm.SymmetricAllReduce(xs[0], ctx, get_codec("fp32"), algorithm="oneshot")
+    worst, same = 0.0, True
+    for it in range(60):
+        x = xs[it % 4]
+        ref = x.clone()
+        dist.all_reduce(ref)
+        if (it + rank) % 3 == 0:
+            torch.cuda._sleep(2_000_000)                 # ~1 ms of skew on a rotating subset of ranks
+        ar.buffer.copy_(x)
+        ar.all_reduce_()
+        got = ar.buffer.clone()
+        worst = max(worst, (got - ref).abs().max().item())
+        lst = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(lst, got)
+        same = same and all(torch.equal(lst[0], t) for t in lst)
+    ar.check_abort()
+    dist.barrier(device_ids=[rank])
+    if rank == 0:
+        q.put((worst, same, float(xs[0].abs().max())))
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_oneshot_allreduce_survives_rank_skew():
+    world = min(torch.cuda.device_count(), 8)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_oneshot_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    worst, same, scale = q.get(timeout=200)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert worst <= 1e-5 * scale * world, worst
+    assert same
