@@ -509,7 +509,11 @@ static cudaError_t head_ce_raise_smem_limit() {
   int optin = 0;
   e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(b200::head_ce_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  cudaFuncAttributes fa{};
+  e = cudaFuncGetAttributes(&fa, b200::head_ce_kernel<KMAX>);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b200::head_ce_kernel<KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           optin - (int)fa.sharedSizeBytes);   // the opt-in limit covers static + dynamic
   if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
   return e;
 }

@@ -80,6 +80,7 @@ class Trainer:
             nat.setup_overlap(buckets, timeout_s=cfg.timeout_s)
             self.overlap = nat
         self._reduced = False         # the pending gradients were already all-reduced under backward
+        self.comm_stats: Dict[str, float] = {}
         self.optimizer = build_optimizer(self.model, cfg)
         self.optimizer.rebind_grad(self.model.flat["grad"])
 
@@ -221,6 +222,50 @@ class Trainer:
             self.sync.after_step()
         self.pending = 0
 
+    @torch.no_grad()
+    def calibrate_comm(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, reps: int = 3) -> Dict[str, float]:
+        """Measure what the gradient exchange costs and how much of it backward hides (metrics.jsonl fields
+        ``comm_ms``, ``comm_exposed_ms``, ``overlap_pct``; the reference only prints wall-clock phase times,
+        R:265-440).  ``comm_ms``: the whole-buffer all-reduce on its own; ``comm_exposed_ms``: micro-batch with
+        the bucketed exchange minus micro-batch without.  Device time, max over ranks.  Leaves parameters,
+        gradients, BN buffers and the optimizer untouched.  Collective: every rank must call it."""
+        nat = getattr(self.sync, "native", None)
+        if nat is None or self.device.type != "cuda":
+            return {}
+        flat_g = self.model.flat["grad"]
+        saved = flat_g.clone()
+        bufs = [b.clone() for b in self.model.buffers()]
+
+        def timed(fn) -> float:
+            fn()                                           # warm-up (graph capture, lazy loads)
+            torch.cuda.synchronize(self.device)
+            self.ctx.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize(self.device)
+            return pdist.all_reduce_max_time(a.elapsed_time(b) / reps, self.ctx)
+
+        out = {"comm_ms": timed(lambda: nat.all_reduce_())}
+        if self.overlap is not None and self.engine_kind == "native":
+            def with_ov():
+                self.micro_step(images_u8, labels_u8, sync_now=True)
+                self._reduced = False
+            t_ov = timed(with_ov)
+            t_plain = timed(lambda: self.micro_step(images_u8, labels_u8, sync_now=False))
+            out["comm_exposed_ms"] = max(t_ov - t_plain, 0.0)
+            out["overlap_pct"] = 100.0 * max(0.0, 1.0 - out["comm_exposed_ms"] / max(out["comm_ms"], 1e-9))
+        else:
+            out["comm_exposed_ms"] = out["comm_ms"]
+            out["overlap_pct"] = 0.0
+        flat_g.copy_(saved)
+        for b, keep in zip(self.model.buffers(), bufs):
+            b.copy_(keep)
+        self.comm_stats = out
+        return out
+
     def check_peers(self) -> None:
         """Raise ``PeerLost`` if a bounded device-side wait of the gradient exchange gave up (a peer stalled
         or died; the reference would hang forever in ``recv``, R:98).  Rank 0 first writes
@@ -335,13 +380,17 @@ class Trainer:
         cfg = self.cfg
         self.log.header(count_parameters(self.model), resumed=bool(cfg.resume))
         last: Dict[str, float] = {}
+        if self.sync.native is not None and len(self.train_set) >= cfg.batch_size:
+            b = cfg.batch_size
+            self.calibrate_comm(self.train_set.images[:b].to(self.device), self.train_set.labels[:b].to(self.device))
         while self.epoch < cfg.epochs:
             last = self.train_epoch()
             if cfg.eval_holdout and self.hold_set is not None:
                 last.update(self.evaluate())
             self.log.epoch(self.epoch, last["mean_loss"], last["mean_accuracy"], last["epoch_s"],
                            last["step_ms"], last["sync_ms"],
-                           {k: v for k, v in last.items() if k.startswith(("eval_", "tiles_"))})
+                           dict({k: v for k, v in last.items() if k.startswith(("eval_", "tiles_", "optimizer_"))},
+                                **self.comm_stats))
             if cfg.sample_images:
                 self.dump_samples()
             self.epoch += 1
