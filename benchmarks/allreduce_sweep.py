@@ -41,6 +41,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=int, default=512)
     ap.add_argument("--out", default="")
+    ap.add_argument("--grid-sweep", action="store_true", help="also time the NVLS kernel at 32..256 CTAs")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -53,7 +54,8 @@ def main():
         x = torch.randn(n, device="cuda")
         row = {"bytes": size, "world": world}
         row["nccl_ms"] = timed(lambda: dist.all_reduce(x), 20, world, local)
-        variants = [("twoshot", "fp32"), ("twoshot", "bf16")]
+        # lossy codecs go through the quantize-on-send push kernel (amax included for the scaled ones)
+        variants = [("twoshot", "fp32"), ("twoshot", "bf16"), ("twoshot", "int8s")]
         if size <= symm.ONESHOT_MAX_BYTES:
             variants.append(("oneshot", "fp32"))
         probe = symm.SymmetricAllReduce(x, ctx, get_codec("fp32"), algorithm="twoshot")
@@ -64,6 +66,10 @@ def main():
             try:
                 ar = symm.SymmetricAllReduce(x, ctx, get_codec(codec), algorithm=algo)
                 row[f"{algo}_{codec}_ms"] = timed(lambda: ar.all_reduce_(), 20, world, local)
+                if algo == "nvls" and a.grid_sweep and size >= (16 << 20):
+                    for blocks in (32, 64, 128, 256):      # CTAs of 512 threads, 4 x 16 B in flight per thread
+                        ar.blocks = blocks
+                        row[f"nvls_fp32_b{blocks}_ms"] = timed(lambda: ar.all_reduce_(), 20, world, local)
                 del ar
             except Exception as exc:                      # keep sweeping
                 row[f"{algo}_{codec}_err"] = str(exc)[:80]

@@ -260,6 +260,24 @@ void allreduce(at::IntArrayRef wire_ptrs, at::IntArrayRef grad_ptrs, at::IntArra
                        cur()), "allreduce");
 }
 
+void allreduce_push(at::IntArrayRef inbox_ptrs, at::IntArrayRef grad_ptrs, at::IntArrayRef signal_ptrs,
+                    at::IntArrayRef mult_ptrs, OptT scale, std::string codec, int64_t rank, int64_t n_elems,
+                    double post_scale, int64_t epoch, int64_t blocks) {
+  const int world = (int)inbox_ptrs.size();
+  TORCH_CHECK(world >= 2 && world <= 16 && (int)grad_ptrs.size() == world && (int)signal_ptrs.size() == world &&
+              (mult_ptrs.empty() || (int)mult_ptrs.size() == world), "allreduce_push: bad pointer lists");
+  void* ip[16]; float* gp[16]; unsigned int* sp[16]; float* mp[16];
+  for (int r = 0; r < world; ++r) {
+    ip[r] = reinterpret_cast<void*>(inbox_ptrs[r]);
+    gp[r] = reinterpret_cast<float*>(grad_ptrs[r]);
+    sp[r] = reinterpret_cast<unsigned int*>(signal_ptrs[r]);
+    mp[r] = mult_ptrs.empty() ? nullptr : reinterpret_cast<float*>(mult_ptrs[r]);
+  }
+  ok(b200seg_allreduce_push(ip, gp, sp, mult_ptrs.empty() ? nullptr : mp, scale.has_value() ? f32(*scale) : nullptr,
+                            codec_id(codec), (int)rank, world, n_elems, (float)post_scale, (unsigned int)epoch,
+                            (int)blocks, cur()), "allreduce_push");
+}
+
 void allreduce_nvls(at::IntArrayRef signal_ptrs, int64_t multicast_ptr, int64_t rank, int64_t n_elems,
                     double post_scale, int64_t epoch, int64_t blocks) {
   const int world = (int)signal_ptrs.size();
@@ -370,6 +388,8 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("allreduce(int[] wire_ptrs, int[] grad_ptrs, int[] signal_ptrs, int[] mult_ptrs, int rank, int n_elems, "
         "int wire_kind, float post_scale, int epoch, Tensor(a!)? oneshot_out, int blocks) -> ()", &allreduce);
   m.def("write_mult(Tensor scale, float levels, Tensor(a!) out) -> ()", &write_mult);
+  m.def("allreduce_push(int[] inbox_ptrs, int[] grad_ptrs, int[] signal_ptrs, int[] mult_ptrs, Tensor? scale, str codec, "
+        "int rank, int n_elems, float post_scale, int epoch, int blocks) -> ()", &allreduce_push);
   m.def("allreduce_nvls(int[] signal_ptrs, int multicast_ptr, int rank, int n_elems, float post_scale, int epoch, "
         "int blocks) -> ()", &allreduce_nvls);
   m.def("peer_barrier(int[] signal_ptrs, int rank, int epoch) -> ()", &peer_barrier);

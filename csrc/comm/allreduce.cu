@@ -254,6 +254,128 @@ __global__ void barrier_kernel(PeerPtrs pp, int rank, int world, uint32_t epoch,
   cross_gpu_barrier(pp, rank, world, epoch, timeout_ns);
 }
 
+// ---- quantize-on-send two-shot ---------------------------------------------------------------------
+// The lossy wire codecs used to cost a separate encode pass over the whole gradient (read 4 B, write 1-2 B
+// per element) before an all-reduce that then PULLED the encoded bytes from the peers.  Here the sender
+// quantizes in registers and PUSHES: rank s reads slice p of its own fp32 gradient, encodes it and stores it
+// straight into rank p's inbox over NVLink (slot s); after one barrier rank p dequantizes the W slots of its
+// slice, adds them in fixed rank order in fp32 (identical bits everywhere, R:402-433) and stores the result
+// into every rank's fp32 gradient buffer.  No encode kernel, no write_mult kernel: the only extra launch a
+// lossy codec costs is the global max-abs (R:451-463 does that with one host sync per tensor).
+// Bytes over NVLink per GPU: (W-1)/W * S/2 (16-bit) or S/4 (8-bit) in, (W-1)/W * S out.
+template <int CODEC> struct PushWire;      // codec ids of csrc/elem/codec.cu
+template <> struct PushWire<1> { static constexpr int V = 8; };    // bf16
+template <> struct PushWire<2> { static constexpr int V = 8; };    // fp16
+template <> struct PushWire<3> { static constexpr int V = 8; };    // q201: round(g/max*100) as fp16
+template <> struct PushWire<4> { static constexpr int V = 16; };   // q21:  round(g/max*10) as int8
+template <> struct PushWire<5> { static constexpr int V = 16; };   // int8s
+template <> struct PushWire<6> { static constexpr int V = 16; };   // fp8 e4m3
+
+template <int CODEC>
+__device__ __forceinline__ uint4 push_encode(const float* f, float s, float levels) {
+  constexpr int V = PushWire<CODEC>::V;
+  uint4 out;
+  if (CODEC == 1) {
+    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&out);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+  } else if (CODEC == 2 || CODEC == 3) {
+    __half2* o = reinterpret_cast<__half2*>(&out);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float a = f[2 * j], b = f[2 * j + 1];
+      if (CODEC == 3) {     // (g / max) * S, rounded, as R:487; IEEE division and product for bit parity with torch
+        a = (s > 0.f) ? rintf(__fmul_rn(__fdiv_rn(a, s), levels)) : 0.f;
+        b = (s > 0.f) ? rintf(__fmul_rn(__fdiv_rn(b, s), levels)) : 0.f;
+      }
+      o[j] = __floats2half2_rn(a, b);
+    }
+  } else if (CODEC == 4 || CODEC == 5) {
+    int8_t* o = reinterpret_cast<int8_t*>(&out);
+#pragma unroll
+    for (int j = 0; j < V; ++j) o[j] = (s > 0.f) ? (int8_t)rintf(__fmul_rn(__fdiv_rn(f[j], s), levels)) : (int8_t)0;
+  } else {
+    __nv_fp8_e4m3* o = reinterpret_cast<__nv_fp8_e4m3*>(&out);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float q = (s > 0.f) ? __fmul_rn(__fdiv_rn(f[j], s), levels) : 0.f;
+      o[j] = __nv_fp8_e4m3(fminf(fmaxf(q, -448.f), 448.f));
+    }
+  }
+  return out;
+}
+
+template <int CODEC, typename WT>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_push_kernel(PeerPtrs pp, const float* __restrict__ my_scale, float levels, int rank, int world, size_t n_vec,
+                      float post_scale, uint32_t epoch, unsigned long long timeout_ns) {
+  constexpr int V = PushWire<CODEC>::V;
+  const size_t per = (n_vec + world - 1) / world;                 // vectors per slice
+  const float s = my_scale != nullptr ? *my_scale : 1.f;
+  // what peers multiply my payload by; EVERY CTA writes it (same value): the barrier below pairs CTA b with the
+  // CTAs b of the other ranks only, so CTA b must not depend on a store made by some other CTA of a peer
+  if (threadIdx.x == 0 && pp.mult[rank] != nullptr)
+    *const_cast<float*>(pp.mult[rank]) = (my_scale != nullptr && levels > 0.f) ? __fdiv_rn(s, levels) : 1.f;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+  const float4* mine = reinterpret_cast<const float4*>(pp.grad[rank]);
+  // phase A: quantize my gradient slice by slice and push slice p into rank p's inbox, slot `rank`
+  for (int k = 0; k < world; ++k) {
+    const int dst = (rank + k) % world;                             // stagger the peers
+    const size_t v0 = (size_t)dst * per;
+    const size_t v1 = v0 + per < n_vec ? v0 + per : n_vec;
+    uint4* inbox = reinterpret_cast<uint4*>(const_cast<void*>(pp.wire[dst])) + (size_t)rank * per;
+    for (size_t i = v0 + tid; i < v1; i += nthr) {
+      float f[V];
+#pragma unroll
+      for (int q4 = 0; q4 < V / 4; ++q4) {
+        const float4 t = mine[i * (V / 4) + q4];
+        f[4 * q4] = t.x; f[4 * q4 + 1] = t.y; f[4 * q4 + 2] = t.z; f[4 * q4 + 3] = t.w;
+      }
+      inbox[i - v0] = push_encode<CODEC>(f, s, levels);
+    }
+  }
+  if (!cross_gpu_barrier(pp, rank, world, epoch, timeout_ns)) return;   // every slot of my inbox has landed
+  float mult[kMaxRanks];
+#pragma unroll
+  for (int r = 0; r < kMaxRanks; ++r)
+    mult[r] = (r < world && pp.mult[r] != nullptr) ? *reinterpret_cast<const volatile float*>(pp.mult[r]) : 1.f;
+  // phase B: dequantize the W slots of my slice, fp32 sum in rank order, store into every rank's gradient
+  const size_t v0 = (size_t)rank * per;
+  const size_t v1 = v0 + per < n_vec ? v0 + per : n_vec;
+  const void* my_inbox = pp.wire[rank];
+  for (size_t i = v0 + tid; i < v1; i += nthr) {
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    constexpr int G = V == 16 ? 4 : 8;                     // slots loaded before any is used (register budget)
+    float f[G][V];
+#pragma unroll
+    for (int r0 = 0; r0 < kMaxRanks; r0 += G) {
+      if (r0 >= world) break;
+#pragma unroll
+      for (int r = 0; r < G; ++r)
+        if (r0 + r < world) Wire<WT>::load(my_inbox, (size_t)(r0 + r) * per + (i - v0), f[r]);
+#pragma unroll
+      for (int r = 0; r < G; ++r) {
+        if (r0 + r < world) {
+          const float m = mult[r0 + r];
+#pragma unroll
+          for (int j = 0; j < V; ++j) acc[j] = fmaf(f[r][j], m, acc[j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] *= post_scale;
+    for (int r = 0; r < world; ++r) {
+      float4* dstp = reinterpret_cast<float4*>(pp.grad[(rank + r) % world]);
+#pragma unroll
+      for (int q4 = 0; q4 < V / 4; ++q4)
+        dstp[i * (V / 4) + q4] = make_float4(acc[4 * q4], acc[4 * q4 + 1], acc[4 * q4 + 2], acc[4 * q4 + 3]);
+    }
+  }
+  cross_gpu_barrier(pp, rank, world, epoch + 1, timeout_ns);        // all slices have landed everywhere
+}
+
 // Registered multicast alias of the gradient buffer (fused wgrad -> all-reduce, see grad_red_add).
 static const char* g_mc_local = nullptr;
 static long long g_mc_bytes = 0;
@@ -337,6 +459,42 @@ extern "C" int b200seg_allreduce(const void* const* wire_ptrs, float* const* gra
     case 4: return launch_ar<__nv_fp8_e4m3>(pp, rank, world, (size_t)n_elems, post_scale, epoch, oneshot_out, blocks, st);
   }
   return (int)cudaErrorInvalidValue;
+}
+
+// Quantize-on-send two-shot.  codec: 1 bf16, 2 fp16, 3 q201, 4 q21, 5 int8s, 6 fp8 (ids of b200seg_codec_*).
+// inbox_ptrs[r]: rank r's inbox, n_elems wire elements (rank p's inbox holds slot s = rank s's copy of slice p);
+// grad_ptrs[r]: rank r's fp32 gradient buffer (source on this rank, destination on all); mult_ptrs[r]: rank r's
+// multiplier slot (written by this kernel); scale: this rank's global max-abs (device), NULL for bf16 / fp16.
+// n_elems % 64 == 0.  Consumes two epochs.
+extern "C" int b200seg_allreduce_push(void* const* inbox_ptrs, float* const* grad_ptrs, unsigned int* const* signal_ptrs,
+                                      float* const* mult_ptrs, const float* scale, int codec, int rank, int world,
+                                      long long n_elems, float post_scale, unsigned int epoch, int blocks,
+                                      cudaStream_t st) {
+  if (world < 2 || world > kMaxRanks || (n_elems % 64) || blocks < 1 || blocks > b200seg_allreduce_max_blocks() ||
+      codec < 1 || codec > 6)
+    return (int)cudaErrorInvalidValue;
+  PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) {
+    pp.wire[r] = inbox_ptrs[r];
+    pp.grad[r] = grad_ptrs[r];
+    pp.signal[r] = signal_ptrs[r];
+    pp.mult[r] = mult_ptrs ? mult_ptrs[r] : nullptr;
+  }
+  const float levels = codec == 3 ? 100.f : (codec == 4 ? 10.f : (codec == 5 ? 127.f : (codec == 6 ? 448.f : 0.f)));
+  const unsigned long long to = g_comm_timeout_ns;
+#define B200_PUSH(C, WT)                                                                                         \
+  allreduce_push_kernel<C, WT><<<blocks, kArThreads, 0, st>>>(pp, scale, levels, rank, world,                    \
+                                                             (size_t)n_elems / PushWire<C>::V, post_scale, epoch, to)
+  switch (codec) {
+    case 1: B200_PUSH(1, __nv_bfloat16); break;
+    case 2: B200_PUSH(2, __half); break;
+    case 3: B200_PUSH(3, __half); break;
+    case 4: B200_PUSH(4, int8_t); break;
+    case 5: B200_PUSH(5, int8_t); break;
+    case 6: B200_PUSH(6, __nv_fp8_e4m3); break;
+  }
+#undef B200_PUSH
+  return (int)cudaGetLastError();
 }
 
 // NVLS variant (fp32 wire only).  `multicast_ptr` comes from the symmetric-memory rendezvous; 0 means

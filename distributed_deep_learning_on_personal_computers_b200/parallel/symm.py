@@ -76,7 +76,8 @@ class SymmetricAllReduce:
         self.h_wire = None
         fp8 = getattr(torch, "float8_e4m3fn", None)
         if codec.name != "fp32":
-            self.wire = symm_mem.empty(self.n * codec.wire_bytes, dtype=torch.uint8, device=dev)
+            # + slack: the push kernel's inbox holds world slots of ceil(vectors / world) 16-byte vectors each
+            self.wire = symm_mem.empty(self.n * codec.wire_bytes + 4096, dtype=torch.uint8, device=dev)
             self.wire.zero_()
             self.h_wire = symm_mem.rendezvous(self.wire, self.group)
             self.wire_kind = 4 if (fp8 is not None and codec.wire_dtype == fp8) else _WIRE_KIND[codec.wire_dtype]
@@ -105,8 +106,10 @@ class SymmetricAllReduce:
         if algorithm == "nvls" and not (self.multicast_ptr and codec.name == "fp32"):
             raise RuntimeError("NVLS all-reduce needs multicast support and the fp32 codec")
         self.algorithm = algorithm
+        # lossy codecs: quantize-on-send push kernel (B200SEG_PUSH=0: the older encode pass + pull two-shot)
+        self.push = codec.name != "fp32" and algorithm == "twoshot" and os.environ.get("B200SEG_PUSH", "1") != "0"
         self.oneshot_out: Optional[torch.Tensor] = None
-        if self.n * 4 <= ONESHOT_MAX_BYTES and self.algorithm != "nvls" or self.algorithm == "oneshot":
+        if (self.n * 4 <= ONESHOT_MAX_BYTES and self.algorithm != "nvls" and not self.push) or self.algorithm == "oneshot":
             self.oneshot_out = torch.empty(self.n, dtype=torch.float32, device=dev)
         # Fused mode: the first `fused_bulk_elems` floats (the conv / convT weight gradients) are reduced
         # by the wgrad kernels themselves -- their epilogues add through the multicast alias, i.e. into
@@ -201,6 +204,17 @@ class SymmetricAllReduce:
         from ..ops import functional as Fn
         ops = torch.ops.b200seg
         c = self.codec
+        epoch = self.epoch
+        self.epoch += 2
+        if c.name != "fp32" and self.push:
+            # quantize-on-send: the all-reduce kernel encodes in registers and pushes into the owners' inboxes;
+            # a lossy codec costs one extra launch (the global max-abs), not an encode pass
+            scale = Fn.codec_amax(self.buffer_full) if c.needs_scale else None
+            ops.allreduce_push(self.wire_ptrs, self.grad_ptrs, self.sig_ptrs,
+                               [p + self.mult_off for p in self.sig_ptrs], scale, c.name, self.ctx.rank, self.n,
+                               float(post_scale), epoch, self.blocks)
+            Fn._tick()
+            return self.buffer
         if c.name != "fp32":
             scale = Fn.codec_amax(self.buffer_full) if c.needs_scale else torch.ones((), device=self.buffer.device)
             ops.codec_encode(self.buffer_full, scale, self.wire, c.name)
@@ -209,8 +223,6 @@ class SymmetricAllReduce:
                 levels = c.levels if c.levels is not None else 448.0
                 ops.write_mult(scale, float(levels), self.mult_slot)
                 Fn._tick()
-        epoch = self.epoch
-        self.epoch += 2
         if self.fused_bulk:
             if self.tail_n:
                 off = self.fused_bulk * 4

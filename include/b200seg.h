@@ -97,6 +97,14 @@ int b200seg_allreduce(const void* const* wire_ptrs, float* const* grad_ptrs,
                       long long n_elems, int wire_kind, float post_scale, unsigned int epoch,
                       float* oneshot_out, int blocks, cudaStream_t st);
 
+/* Quantize-on-send two-shot for the lossy codecs (1 bf16, 2 fp16, 3 q201, 4 q21, 5 int8s, 6 fp8): R:451-496 and
+ * R:513-545 without an encode pass -- the sender quantizes in registers and stores into the owner's inbox over
+ * NVLink, the owner dequantizes, adds in rank order in fp32 and stores fp32 into every rank's gradient buffer.
+ * scale: this rank's max-abs on the device (b200seg_amax), NULL for bf16 / fp16.  n_elems % 64 == 0. */
+int b200seg_allreduce_push(void* const* inbox_ptrs, float* const* grad_ptrs, unsigned int* const* signal_ptrs,
+                           float* const* mult_ptrs, const float* scale, int codec, int rank, int world,
+                           long long n_elems, float post_scale, unsigned int epoch, int blocks, cudaStream_t st);
+
 /* NVLS: the NVSwitch performs the addition (multimem.ld_reduce / multimem.st on the multicast mapping of
  * the symmetric fp32 buffer).  multicast_ptr == NULL -> cudaErrorInvalidValue (use b200seg_allreduce). */
 int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* multicast_ptr, int rank, int world,
