@@ -1,11 +1,11 @@
 // Weight gradient of the 3x3 conv for 64-channel output tiles, "row-pair" form (W >= 64):
 //     dW[co][(r,s)][ci] += sum_p dy[p][co] * x[p + (r-1, s-1)][ci]                 (autograd of R:579)
 //
-// Why another kernel: measured on B200 (profiles/ncu_mma_issue.txt), an M = 128, N = 64 tcgen05.mma holds
-// the tensor pipe for 64 cycles -- as long as N = 128.  wgrad_strip_kernel<64> (wgrad_strip.cu) issues
-// exactly that shape (M = two taps x 64 Cin, N = 64 Cout) and therefore tops out at ~half the MMA rate
-// (20 instructions x 64 cycles per 64-pixel step for 576 cycles of math).  Here the roles are swapped so
-// that N is wide:
+// Why another kernel: measured on B200 across three kernel forms (profiles/umma_cost_model.txt), one
+// tcgen05.mma with M = 128, K = 16 occupies the tensor pipe for about N/2 + 32 cycles: N/2 is the math, the 32
+// are a fixed cost per instruction.  wgrad_strip_kernel<64> (wgrad_strip.cu) issues M = two taps x 64 Cin,
+// N = 64 Cout: 20 instructions x 64 cycles per 64-pixel step for 576 cycles of math.  Fewer, wider
+// instructions are what pays, so here the roles are swapped and N is made as wide as the data allows:
 //
 //     A (M = 128) = the dy tiles of TWO consecutive image rows stacked ([64 px][64 co] each; the second block
 //                   is found through the descriptor's leading-offset field = one ring stage),
@@ -14,8 +14,9 @@
 //
 //   For input row s:   G1:  [dy(s-1) ; dy(s)]  x  strip(s)   ->  D1[(j, co)][(dw, ci)]   j=0: tap dh=+1, j=1: tap dh=0
 //                      G2:  [dy(s+1) ;  --  ]  x  strip(s)   ->  D2[co][(dw, ci)]        tap dh=-1 (upper 64 lanes unused)
-//   8 instructions x 96 cycles = 768 cycles per step instead of 1280, and each operand byte is read from
-//   shared memory less often (10 KB per instruction against 96 cycles of math).
+//   8 instructions x (96 + 32) cycles = 1024 cycles per step instead of 1280 (measured: 1080).  A variant with
+//   both operands as row pairs (12 instructions of 128 x 128, three of four quadrants useful) measured 1145, as
+//   the cost model predicts (12 x 96); it is not kept.
 //
 // A CTA walks "spans" of rows exactly like wgrad_strip_kernel (same stream-K split, same ring of 8 stages;
 // stage j of a span carries input row h0-1+j and, from j = 2, the dy tile of row h0+j-2).  At the ends of
