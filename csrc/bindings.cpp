@@ -171,6 +171,31 @@ void prep_input(const Tensor& img, Tensor out) {
   ok(b200seg_prep_input(img.data_ptr<uint8_t>(), img.numel() / img.size(-1), (int)img.size(-1), out.data_ptr(),
                         (int)out.size(-1), cur()), "prep_input");
 }
+void pad_rows(const Tensor& src, Tensor dst) {
+  c10::cuda::CUDAGuard g(dst.device());
+  bf16(src, "src"); bf16(dst, "dst");
+  TORCH_CHECK(src.is_contiguous() && dst.is_contiguous() && src.numel() / src.size(-1) == dst.numel() / dst.size(-1),
+              "pad_rows: contiguous tensors with the same number of rows");
+  ok(b200seg_pad_rows(src.data_ptr(), (int)(src.numel() / src.size(-1)), (int)src.size(-1), dst.data_ptr(),
+                      (int)dst.size(-1), cur()), "pad_rows");
+}
+void unpad_add_zero(Tensor src, Tensor dst) {
+  c10::cuda::CUDAGuard g(dst.device());
+  TORCH_CHECK(src.is_contiguous() && dst.is_contiguous() && src.scalar_type() == at::kFloat &&
+              dst.scalar_type() == at::kFloat && src.numel() / src.size(-1) == dst.numel() / dst.size(-1),
+              "unpad_add_zero: contiguous fp32 tensors with the same number of rows");
+  ok(b200seg_unpad_add_zero(src.data_ptr<float>(), (int)(src.numel() / src.size(-1)), (int)src.size(-1),
+                            dst.data_ptr<float>(), (int)dst.size(-1), cur()), "unpad_add_zero");
+}
+void rows_sum_add(const Tensor& part, int64_t C, Tensor out) {
+  c10::cuda::CUDAGuard g(out.device());
+  TORCH_CHECK(part.dim() >= 2 && part.is_contiguous() && part.scalar_type() == at::kFloat && out.is_contiguous() &&
+              out.scalar_type() == at::kFloat && out.numel() >= C && part.size(-1) >= C, "rows_sum_add");
+  const long long row_stride = part.numel() / part.size(0);
+  ok(b200seg_rows_sum_add(part.data_ptr<float>(), (int)part.size(0), row_stride, (int)C, out.data_ptr<float>(), cur()),
+     "rows_sum_add");
+}
+
 void upsample_fwd(const Tensor& x, Tensor out) {
   c10::cuda::CUDAGuard g(x.device());
   bf16(x, "x"); bf16(out, "out");
@@ -383,6 +408,9 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("codec_decode(Tensor in_bytes, Tensor scale, Tensor(a!) out, str codec, bool accumulate) -> ()",
         &codec_decode);
   m.def("prep_input(Tensor img, Tensor(a!) out) -> ()", &prep_input);
+  m.def("pad_rows(Tensor src, Tensor(a!) dst) -> ()", &pad_rows);
+  m.def("unpad_add_zero(Tensor(a!) src, Tensor(b!) dst) -> ()", &unpad_add_zero);
+  m.def("rows_sum_add(Tensor part, int C, Tensor(a!) out) -> ()", &rows_sum_add);
   m.def("upsample_bilinear2x_fwd(Tensor x, Tensor(a!) out) -> ()", &upsample_fwd);
   m.def("upsample_bilinear2x_bwd(Tensor d_up, Tensor(a!) dx) -> ()", &upsample_bwd);
   m.def("allreduce(int[] wire_ptrs, int[] grad_ptrs, int[] signal_ptrs, int[] mult_ptrs, int rank, int n_elems, "

@@ -101,9 +101,54 @@ upsample2x_bwd_kernel(const __nv_bfloat16* __restrict__ g, long long ld_g, __nv_
   }
 }
 
+// ---- small glue kernels that keep eager ATen ops out of the captured training step -----------------------
+// rows x cin bf16 -> rows x cpad bf16, zero padded (the stem's 3-channel weights as one UMMA K step)
+__global__ void pad_rows_kernel(const __nv_bfloat16* __restrict__ src, int rows, int cin, __nv_bfloat16* __restrict__ dst,
+                                int cpad) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cpad) return;
+  const int r = i / cpad, c = i - r * cpad;
+  dst[i] = c < cin ? src[r * cin + c] : __float2bfloat16(0.f);
+}
+// dst[r][c] += src[r][c] for c < cin, then src := 0 (the padded stem weight gradient folded back and re-armed)
+__global__ void unpad_add_zero_kernel(float* __restrict__ src, int rows, int cpad, float* __restrict__ dst, int cin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cpad) return;
+  const int r = i / cpad, c = i - r * cpad;
+  if (c < cin) dst[r * cin + c] += src[i];
+  src[i] = 0.f;
+}
+// out[c] += sum over rows of part[r * row_stride + c]  (per-CTA column sums -> the transposed conv's bias gradient)
+__global__ void rows_sum_add_kernel(const float* __restrict__ part, int rows, long long row_stride, int C,
+                                    float* __restrict__ out) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int r = lane; r < rows; r += 32) s += part[(size_t)r * row_stride + c];
+  s = warp_sum(s);
+  if (lane == 0) out[c] += s;
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200seg_pad_rows(const void* src, int rows, int cin, void* dst, int cpad, cudaStream_t st) {
+  if (cin > cpad || rows < 1) return (int)cudaErrorInvalidValue;
+  pad_rows_kernel<<<(rows * cpad + 255) / 256, 256, 0, st>>>((const __nv_bfloat16*)src, rows, cin, (__nv_bfloat16*)dst, cpad);
+  return (int)cudaGetLastError();
+}
+extern "C" int b200seg_unpad_add_zero(float* src, int rows, int cpad, float* dst, int cin, cudaStream_t st) {
+  if (cin > cpad || rows < 1) return (int)cudaErrorInvalidValue;
+  unpad_add_zero_kernel<<<(rows * cpad + 255) / 256, 256, 0, st>>>(src, rows, cpad, dst, cin);
+  return (int)cudaGetLastError();
+}
+extern "C" int b200seg_rows_sum_add(const float* part, int rows, long long row_stride, int C, float* out, cudaStream_t st) {
+  if (rows < 1 || C < 1) return (int)cudaErrorInvalidValue;
+  rows_sum_add_kernel<<<(C * 32 + 127) / 128, 128, 0, st>>>(part, rows, row_stride, C, out);
+  return (int)cudaGetLastError();
+}
 
 extern "C" int b200seg_prep_input(const unsigned char* img, long long P, int Cin, void* out, int Cpad,
                                   cudaStream_t st) {

@@ -183,7 +183,8 @@ class NativeEngine:
         sp = st.spec
         w = self._w3(self.flat_lp, sp.name + ".weight")
         if self.stem_pad and sp.name == self.stem:
-            self.stem_w[..., :w.shape[3]].copy_(w)
+            torch.ops.b200seg.pad_rows(w, self.stem_w)       # 3 -> 16 channels, zero padded (no ATen op in the graph)
+            Fn._tick()
             w = self.stem_w
         bias = self._seg(self.flat_p, sp.name + ".bias")
         # the conv bias is NOT added by the conv: BatchNorm absorbs it (see ops.reference.bn_finalize)
@@ -208,9 +209,10 @@ class NativeEngine:
                             self._seg(self.flat_g, sp.name + ".bias"), st.dy)
         dw = self._w3(self.flat_g, sp.name + ".weight")
         if self.stem_pad and sp.name == self.stem:
-            self.stem_dw.zero_()
+            # stem_dw is zero on entry (allocated zeroed, re-zeroed by the fold below)
             Fn.conv3x3_wgrad(st.x, st.dy, self.stem_dw, impl=self.conv_impl)
-            dw.add_(self.stem_dw[..., :dw.shape[3]])
+            torch.ops.b200seg.unpad_add_zero(self.stem_dw, dw)
+            Fn._tick()
         else:
             bucket = self._arm(sp.name + ".weight", sp.cin, sp.cout)
             Fn.conv3x3_wgrad(st.x, st.dy, dw, impl=self.conv_impl)

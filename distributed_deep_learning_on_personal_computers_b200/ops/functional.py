@@ -189,13 +189,13 @@ def convT2x2_bwd(x, d_up, w_param, w_lp, dw_param, dbias, dx, impl=None, d_up_pa
         cout = cout4 // 4
         if _use_tc(cin, cout, impl):
             if d_up_partials is not None:        # column sums of d_up already came out of the dgrad that wrote it
-                dbias.add_(d_up_partials[:, 0, :cout].sum(0))
-                _tick(2)
+                _ops().rows_sum_add(d_up_partials, cout, dbias)
+                _tick()
             else:
                 part = torch.empty(_ops().stats_rows(), 2, cout, dtype=torch.float32, device=x.device)
                 _ops().channel_stats(d_up, part)
-                dbias.add_(part[:, 0, :].sum(0))
-                _tick(3)
+                _ops().rows_sum_add(part, cout, dbias)
+                _tick(2)
             _ops().convT2x2_bwd(x, d_up, w_lp, _flat_of(dw_param).reshape(4 * cout, cin), dx)
             return
         wl = w_lp.view(2, 2, cout, cin).permute(3, 2, 0, 1)               # logical (Cin,Cout,2,2)

@@ -79,6 +79,13 @@ int b200seg_upsample2x_fwd(const void* x, long long ld_x, void* out, long long l
 int b200seg_upsample2x_bwd(const void* g, long long ld_g, void* dx, long long ld_x, int N, int h, int w,
                            int C, cudaStream_t st);
 
+/* glue that keeps eager framework ops out of the captured step (no reference counterpart: autograd does this
+ * bookkeeping there): pad bf16 rows cin -> cpad with zeros; dst[r][c<cin] += src[r][c], src := 0;
+ * out[c] += sum_r part[r * row_stride + c]. */
+int b200seg_pad_rows(const void* src, int rows, int cin, void* dst, int cpad, cudaStream_t st);
+int b200seg_unpad_add_zero(float* src, int rows, int cpad, float* dst, int cin, cudaStream_t st);
+int b200seg_rows_sum_add(const float* part, int rows, long long row_stride, int C, float* out, cudaStream_t st);
+
 /* ---- gradient all-reduce over NVLink peer memory: R:255-440, R:443-556 -------------------------
  * Pointer arrays are indexed by rank and hold addresses valid in THIS process (symmetric memory).
  * wire_kind: 0 fp32, 1 bf16, 2 fp16 (also q201), 3 int8 (q21, int8s), 4 fp8.  n_elems % 16 == 0.
