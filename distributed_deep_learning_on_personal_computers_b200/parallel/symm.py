@@ -99,13 +99,18 @@ class SymmetricAllReduce:
             self.multicast_ptr = 0
         import os
         if algorithm == "auto":
-            # NVLS measured fastest at every size on 8 GPUs (profiles/allreduce_sweep_8gpu.txt);
-            # B200SEG_NVLS=0 forces the peer load/store kernels.
+            # Measured (profiles/allreduce_sweep_{2,4,8}gpu.txt): with 4 or more ranks the in-switch reduction
+            # wins at every size; between two GPUs the peer load/store kernel does (622 vs 399 GB/s bus at 256 MB:
+            # the switch has nothing to save with one peer).  B200SEG_NVLS=0 forces the peer kernels.
             algorithm = "nvls" if (os.environ.get("B200SEG_NVLS", "1") != "0" and self.multicast_ptr
-                                   and codec.name == "fp32") else "twoshot"
+                                   and codec.name == "fp32" and ctx.world_size > 2) else "twoshot"
         if algorithm == "nvls" and not (self.multicast_ptr and codec.name == "fp32"):
             raise RuntimeError("NVLS all-reduce needs multicast support and the fp32 codec")
         self.algorithm = algorithm
+        if algorithm == "nvls":
+            # multimem kernels saturate the fabric with few CTAs (4 x 16 B in flight per thread); more CTAs only
+            # add contention: 32 CTAs 810 / 708 / 481 GB/s bus at 256 / 64 / 16 MB on 8 GPUs against 748 / 561 / 384 with 256
+            self.blocks = int(os.environ.get("B200SEG_NVLS_BLOCKS", "32"))
         # lossy codecs: quantize-on-send push kernel (B200SEG_PUSH=0: the older encode pass + pull two-shot)
         self.push = codec.name != "fp32" and algorithm == "twoshot" and os.environ.get("B200SEG_PUSH", "1") != "0"
         self.oneshot_out: Optional[torch.Tensor] = None
