@@ -196,6 +196,12 @@ void rows_sum_add(const Tensor& part, int64_t C, Tensor out) {
      "rows_sum_add");
 }
 
+void set_error_record(const Tensor& pinned) {
+  TORCH_CHECK(pinned.is_pinned() && pinned.scalar_type() == at::kInt && pinned.numel() >= 8 && pinned.is_contiguous(),
+              "set_error_record: a pinned int32 tensor of >= 8 elements");
+  ok(b200seg_set_error_record(reinterpret_cast<unsigned int*>(pinned.data_ptr<int>())), "set_error_record");
+}
+
 void upsample_fwd(const Tensor& x, Tensor out) {
   c10::cuda::CUDAGuard g(x.device());
   bf16(x, "x"); bf16(out, "out");
@@ -408,6 +414,7 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("codec_decode(Tensor in_bytes, Tensor scale, Tensor(a!) out, str codec, bool accumulate) -> ()",
         &codec_decode);
   m.def("prep_input(Tensor img, Tensor(a!) out) -> ()", &prep_input);
+  m.def("set_error_record(Tensor pinned) -> ()", &set_error_record);
   m.def("pad_rows(Tensor src, Tensor(a!) dst) -> ()", &pad_rows);
   m.def("unpad_add_zero(Tensor(a!) src, Tensor(b!) dst) -> ()", &unpad_add_zero);
   m.def("rows_sum_add(Tensor part, int C, Tensor(a!) out) -> ()", &rows_sum_add);

@@ -1620,3 +1620,21 @@ extern "C" int b200conv_convT_wgrad(const void* x, long long ld_x, const void* d
                                     int N, int h, int w_, int Cin, int Cout, cudaStream_t st) {
   return run_wgrad(1, x, ld_x, d_up, ld_g, dw, N, h, w_, Cin, Cout, st);
 }
+
+// Points this translation unit's error record (umma.cuh mbar_timeout_trap) at mapped host memory.
+extern "C" int b200conv_set_error_record_tc(unsigned int* host_mapped) {
+  return (int)cudaMemcpyToSymbol(b200::g_error_record, &host_mapped, sizeof(host_mapped));
+}
+
+extern "C" int b200conv_set_error_record_strip(unsigned int* host_mapped);
+extern "C" int b200conv_set_error_record_pair(unsigned int* host_mapped);
+// `host_mapped`: >= 8 words of pinned, device-mapped host memory (or NULL to disable), set per device with that
+// device current.  A bounded mbarrier wait of the tcgen05 kernels that times out stores {0xB200DEAD, barrier
+// address, parity, CTA, thread} there before it traps, so the host can still say WHICH wait failed after the
+// context is gone.
+extern "C" int b200seg_set_error_record(unsigned int* host_mapped) {
+  int e = b200conv_set_error_record_tc(host_mapped);
+  if (e == 0) e = b200conv_set_error_record_strip(host_mapped);
+  if (e == 0) e = b200conv_set_error_record_pair(host_mapped);
+  return e;
+}

@@ -311,3 +311,8 @@ extern "C" int b200conv_wgrad_pair(const void* x, long long ld_x, const void* dy
   }
   return (int)launch_k(wgrad_pair_kernel, grid, kWpThreads, kWpSmem, st, mx, mdy, p);
 }
+
+// Points this translation unit's error record (umma.cuh mbar_timeout_trap) at mapped host memory.
+extern "C" int b200conv_set_error_record_pair(unsigned int* host_mapped) {
+  return (int)cudaMemcpyToSymbol(b200::g_error_record, &host_mapped, sizeof(host_mapped));
+}

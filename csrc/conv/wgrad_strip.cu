@@ -359,3 +359,8 @@ extern "C" int b200conv_wgrad_strip(const void* x, long long ld_x, const void* d
   if (rc != 0) return rc;
   return b200conv_wgrad_taps(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, 8, 1, st);   // tap (2,2)
 }
+
+// Points this translation unit's error record (umma.cuh mbar_timeout_trap) at mapped host memory.
+extern "C" int b200conv_set_error_record_strip(unsigned int* host_mapped) {
+  return (int)cudaMemcpyToSymbol(b200::g_error_record, &host_mapped, sizeof(host_mapped));
+}

@@ -15,6 +15,12 @@ def main(argv=None) -> int:
         last = trainer.fit()
         if trainer.ctx.is_coordinator:
             print(json.dumps({k: v for k, v in last.items()}, default=float))
+    except Exception:
+        from .ops import loader
+        note = loader.last_device_error()          # which barrier wait timed out, if a kernel trapped
+        if note:
+            print("device error record:", note, file=sys.stderr)
+        raise
     finally:
         trainer.close()
     return 0

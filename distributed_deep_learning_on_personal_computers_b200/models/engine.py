@@ -70,6 +70,9 @@ class NativeEngine:
             self.flat_lp = self.flat_p.to(self.act_dtype)
         self._params = dict(model.named_parameters())
         self._buffers = dict(model.named_buffers())
+        if self.on_gpu:
+            from ..ops import loader
+            loader.arm_error_record()            # a timed-out barrier wait leaves its address behind before it traps
         self._build()
         self.training = True
         # The stem reads 3 real + 13 zero channels (one UMMA K step).  Its bf16 weights are kept

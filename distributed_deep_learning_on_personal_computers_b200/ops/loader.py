@@ -86,3 +86,23 @@ def library() -> Optional[str]:
 
 def load_error() -> Optional[str]:
     return _load_error
+
+
+_error_record = None
+
+
+def arm_error_record() -> None:
+    """Register a pinned host buffer as the tcgen05 kernels' error record on the current device (idempotent)."""
+    global _error_record
+    if _error_record is None and library() is not None and torch.cuda.is_available():
+        _error_record = torch.zeros(8, dtype=torch.int32).pin_memory()
+        torch.ops.b200seg.set_error_record(_error_record)
+
+
+def last_device_error() -> Optional[str]:
+    """What a bounded mbarrier wait left behind before it trapped (readable without any CUDA call), or None."""
+    r = _error_record
+    if r is None or (int(r[0]) & 0xFFFFFFFF) != 0xB200DEAD:
+        return None
+    return (f"tcgen05 kernel: mbarrier at shared address 0x{int(r[1]) & 0xFFFFFFFF:x} (parity {int(r[2])}) did not flip; "
+            f"CTA {int(r[3])}, thread {int(r[4])}")

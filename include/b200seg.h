@@ -118,6 +118,11 @@ int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* multicast_pt
                            long long n_elems, float post_scale, unsigned int epoch, int blocks,
                            cudaStream_t st);
 
+/* Error record of the tcgen05 kernels (no reference counterpart): >= 8 words of pinned, device-mapped host memory,
+ * registered per device.  A bounded mbarrier wait that times out writes {0xB200DEAD, barrier address, parity, CTA,
+ * thread} there and then traps; the record outlives the CUDA context. */
+int b200seg_set_error_record(unsigned int* host_mapped);
+
 /* ---- tcgen05 / TMEM / TMA convolutions (csrc/conv): R:579, R:582 (3x3 conv), their autograd
  * backward (dgrad, wgrad), R:607 (ConvTranspose2d k=2 s=2 fused with the concat placement, R:616).
  * Weights are bf16 in the flat-buffer order (Cout,3,3,Cin); dgrad reads them un-transposed as an
