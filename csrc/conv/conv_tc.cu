@@ -500,21 +500,30 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   } else {
     // ===================================== epilogue ==========================================
     if (STRIP && p.epi_private) {
-      // Warp-private pipelines for the 64-column strip layers.  ncu showed the shared epilogue below taking
-      // ~2300 cycles per 128 x 64 tile, most of it in its two CTA-wide barriers and in all 256 threads
-      // waiting for one thread's TMA store (profiles/ncu_mma_issue.txt).  Here warp (q, half) owns rows
-      // 32q..32q+31 x columns 32half..32half+31 of every tile: it reads its TMEM block, packs it into its
-      // OWN 2 KB slab (two slabs, double-buffered) and its lane 0 issues its own 32-pixel x 32-channel TMA
-      // store.  Nothing is shared between warps until the statistics are folded at the very end.
+      // Warp-private pipelines for the strip layers with 64-channel column groups.  ncu showed the shared
+      // epilogue below taking ~2300 cycles per 128 x 64 group, most of it in its two CTA-wide barriers and in all
+      // 256 threads waiting for one thread's TMA store (profiles/ncu_mma_issue.txt).  Here warp (q, half) owns
+      // rows 32q..32q+31 x columns 32half..32half+31 of every 64-column group of every tile: it reads its TMEM
+      // block, packs it into its OWN 2 KB slab (two slabs, double-buffered) and its lane 0 issues its own
+      // 32-pixel x 32-channel TMA store.  Nothing is shared between warps until the statistics are folded at the
+      // very end.  fprop: one group (N = 64), sum and sum of squares in registers.  dgrad: up to three groups
+      // (N = 64 / 128 / 192), column sums only (the transposed conv's bias gradient; the sum-of-squares row of
+      // the partials is written as zero).
+      constexpr int kMaxGrp = B_MN ? 3 : 1;
       const int q = warp & 3, half = (warp - 2) >> 2;
       uint8_t* const slab0 = staging + (size_t)(warp - 2) * 4096;
       const uint32_t slab_a = smem_u32(slab0) + lane * 64;
       const uint32_t a_tfull = smem_u32(bar_tfull);
       const bool stats = p.partials != nullptr;
       const bool has_bias = p.bias != nullptr;
-      float rs_s[32], rs_q[32];
+      const int ngrp = p.block_n >> 6;
+      float rs_s[kMaxGrp][32], rs_q[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) rs_s[j] = rs_q[j] = 0.f;
+      for (int j = 0; j < 32; ++j) {
+        rs_q[j] = 0.f;
+#pragma unroll
+        for (int g = 0; g < kMaxGrp; ++g) rs_s[g][j] = 0.f;
+      }
       int acc = 0, buf = 0;
       uint32_t acc_phase = 0;
       const int acc_n = p.rows2 ? 4 : 2;
@@ -535,81 +544,93 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             mbar_wait_a(a_tfull + 8 * acc, acc_phase);
             tc_fence_after();
           }
-          const uint32_t t_addr = tmem_base + acc * acc_cols + (p.rows4 ? sub * 64 : 0) +
+          const uint32_t t_base = tmem_base + acc * acc_cols + (p.rows4 ? sub * 64 : 0) +
                                   (static_cast<uint32_t>(q * 32) << 16) + ch0;
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(t_addr, r);
-          tmem_ld_wait();
-          tc_fence_before();
-          if (!p.rows4 || sub == 3) {
-            mbar_arrive(&bar_tempty[acc]);                  // accumulator drained (it is in registers now)
-            if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
-          }
-          if (has_bias) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + s_bias[ch0 + j]);
-          }
-          if (stats) {
+          for (int g = 0; g < kMaxGrp; ++g) {
+            if (g < ngrp) {
+              uint32_t r[32];
+              tmem_ld_32x32b_x32(t_base + g * 64, r);
+              tmem_ld_wait();
+              if (g == ngrp - 1) {
+                tc_fence_before();
+                if (!p.rows4 || sub == 3) {
+                  mbar_arrive(&bar_tempty[acc]);            // accumulator drained (it is in registers now)
+                  if (++acc == acc_n) { acc = 0; acc_phase ^= 1; }
+                }
+              }
+              if (has_bias) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float v = __uint_as_float(r[j]);
-              rs_s[j] += v;
-              rs_q[j] = fmaf(v, v, rs_q[j]);
+                for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + s_bias[g * 64 + ch0 + j]);
+              }
+              if (stats) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float v = __uint_as_float(r[j]);
+                  rs_s[g][j] += v;
+                  if (!B_MN) rs_q[j] = fmaf(v, v, rs_q[j]);
+                }
+              }
+              const uint32_t dst = slab_a + buf * 2048;
+#pragma unroll
+              for (int v = 0; v < 4; ++v) {
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+                const bf16x8 pk = pack8(f);
+                const uint32_t* pw = reinterpret_cast<const uint32_t*>(&pk);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + v * 16), "r"(pw[0]), "r"(pw[1]),
+                             "r"(pw[2]), "r"(pw[3])
+                             : "memory");
+              }
+              fence_proxy_async();                          // slab writes -> visible to TMA
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_4d(&map_o2, slab0 + buf * 2048, n_tile * p.block_n + g * 64 + ch0, w0, hb + sub, n0);
+                tma_store_commit();
+                tma_store_wait_read<1>();                   // the slab written NEXT (stored one block ago) is free
+              }
+              __syncwarp();
+              buf ^= 1;
             }
           }
-          const uint32_t dst = slab_a + buf * 2048;
-#pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            float f[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
-            const bf16x8 pk = pack8(f);
-            const uint32_t* pw = reinterpret_cast<const uint32_t*>(&pk);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + v * 16), "r"(pw[0]), "r"(pw[1]),
-                         "r"(pw[2]), "r"(pw[3])
-                         : "memory");
-          }
-          fence_proxy_async();                              // slab writes -> visible to TMA
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_4d(&map_o2, slab0 + buf * 2048, n_tile * 64 + ch0, w0, hb + sub, n0);
-            tma_store_commit();
-            tma_store_wait_read<1>();                       // the slab written NEXT (stored one tile ago) is free
-          }
-          __syncwarp();
-          buf ^= 1;
         }
       }
       if (lane == 0) tma_store_wait_read<0>();
       if (stats) {
         // fold the 128 rows: butterfly inside each warp, then the four warps of a column half through smem
         named_bar_sync(1, kEpiThreads);                     // every slab is free (they are the scratch below)
+        float* red = reinterpret_cast<float*>(staging);    // [group][8 warps][2][32]
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int g = 0; g < kMaxGrp; ++g) {
+          if (g < ngrp) {
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            rs_s[j] += __shfl_xor_sync(0xffffffffu, rs_s[j], o);
-            rs_q[j] += __shfl_xor_sync(0xffffffffu, rs_q[j], o);
-          }
-        }
-        float* red = reinterpret_cast<float*>(staging);    // [8 warps][2][32]
-        if (lane == 0) {
+            for (int j = 0; j < 32; ++j) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            red[((warp - 2) * 2 + 0) * 32 + j] = rs_s[j];
-            red[((warp - 2) * 2 + 1) * 32 + j] = rs_q[j];
+              for (int o = 16; o > 0; o >>= 1) {
+                rs_s[g][j] += __shfl_xor_sync(0xffffffffu, rs_s[g][j], o);
+                if (!B_MN) rs_q[j] += __shfl_xor_sync(0xffffffffu, rs_q[j], o);
+              }
+            }
+            if (lane == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                red[((g * 8 + (warp - 2)) * 2 + 0) * 32 + j] = rs_s[g][j];
+                red[((g * 8 + (warp - 2)) * 2 + 1) * 32 + j] = B_MN ? 0.f : rs_q[j];
+              }
+            }
           }
         }
         named_bar_sync(1, kEpiThreads);
         const int et = threadIdx.x - 64;
-        if (et < 64) {                                      // channel et: column half et / 32, warps 4*half .. 4*half+3
-          const int hf = et >> 5, j = et & 31;
+        if (et < ngrp * 64) {                               // column et: group et / 64, half (et % 64) / 32
+          const int g = et >> 6, hf = (et & 63) >> 5, j = et & 31;
           float sv = 0.f, qv = 0.f;
           for (int wq = 0; wq < 4; ++wq) {
-            sv += red[((hf * 4 + wq) * 2 + 0) * 32 + j];
-            qv += red[((hf * 4 + wq) * 2 + 1) * 32 + j];
+            sv += red[((g * 8 + hf * 4 + wq) * 2 + 0) * 32 + j];
+            qv += red[((g * 8 + hf * 4 + wq) * 2 + 1) * 32 + j];
           }
-          const int col = n_tile * 64 + et;
+          const int col = n_tile * p.block_n + et;
           if (col < p.n_total) {
             p.partials[((size_t)prow * 2 + 0) * p.n_total + col] = sv;
             p.partials[((size_t)prow * 2 + 1) * p.n_total + col] = qv;
@@ -1243,6 +1264,22 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   p.n_total = n_total;
   p.ocb = pick_ocb(mode == 2 ? n_total / 4 : n_total);
   p.block_n = pick_block_n(n_total, p.ocb);
+  {
+    // Strip mode with streamed weights: a 256-column tile re-reads the whole 9 x Kc x 256 filter slice from L2
+    // for every 128-pixel row (0.6 MB per tile at Kc = 128) and cannot use two-row units (TMEM holds two such
+    // accumulators, and they are the double buffer).  Two 128-column N tiles with two-row units read each
+    // weight byte a quarter as often at the price of reading the strips twice.  B200SEG_STRIP_N=256 keeps 256.
+    static int sn_env = -1;
+    if (sn_env < 0) { const char* e = getenv("B200SEG_STRIP_N"); sn_env = (e != nullptr && e[0] == '2') ? 256 : 128; }
+    if (strip && sn_env == 128 && p.ocb == 64 && n_total % 128 == 0 && n_total > 128 && (H % 2 == 0)) p.block_n = 128;
+    // dgrad of a 64-channel-output conv with a wide input (the decoder's first conv, 64 -> 192): three N tiles of
+    // 64 each keep their slice of the filter bank resident (9 x 8 KB) and take the four-row N-merged units, like
+    // the 64 -> 64 layers; as ONE 192-column tile the 216 KB bank is streamed from L2 for every 128 pixels.
+    static int dn_env = -1;
+    if (dn_env < 0) { const char* e = getenv("B200SEG_DGRAD_N64"); dn_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    if (strip && dn_env && mode == 1 && Kc == 64 && p.ocb == 64 && n_total > 64 && n_total <= 256 && (H % 4 == 0))
+      p.block_n = 64;
+  }
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
   p.n_tiles = (n_total + p.block_n - 1) / p.block_n;
   p.groups = p.block_n / p.ocb;
@@ -1274,7 +1311,8 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     p.stage_bytes = ((b_raw + 1023) / 1024) * 1024;        // the ring holds weight tiles only
     // small filter banks (64 -> 64, the stem) stay resident: no weight traffic after the first tile
     const uint32_t bank = 9u * p.kc_per_tap * p.stage_bytes;
-    p.b_resident = (p.n_tiles == 1 && 4 * p.xslot_bytes + 2 * p.staging_bytes + bank <= kSmemBudget) ? 1 : 0;
+    // (a CTA keeps one N tile for its whole life, so its slice of the bank can stay resident with several N tiles)
+    p.b_resident = ((p.n_tiles == 1 || p.block_n == 64) && 4 * p.xslot_bytes + 2 * p.staging_bytes + bank <= kSmemBudget) ? 1 : 0;
     auto fits = [&](int bufs, int xs, int bst) {
       return (long long)bufs * p.staging_bytes + (long long)xs * p.xslot_bytes +
              (p.b_resident ? (long long)bank : (long long)bst * p.stage_bytes) <= (long long)kSmemBudget;
@@ -1291,7 +1329,7 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     // profiles/ncu_mma_issue.txt), so merging is worth up to 2x on the MMA side.  With the warp-private
     // epilogue it pays for fprop as well (64 -> 64 fprop 0.351 -> 0.241 ms, stem 0.271 -> 0.154 ms).
     p.rows4 = (p.b_resident && (rows4_env() == 2 || (rows4_env() == 1 && mode == 1)) && (H % 4 == 0) &&
-               p.block_n == 64 && p.n_total == 64 &&
+               p.block_n == 64 &&
                p.kc_per_tap == 1 && p.stage_bytes == 64u * BK * 2u && fits(1, 6, 0)) ? 1 : 0;
     if (p.rows4) p.staging_bufs = fits(2, 6, 0) ? 2 : 1;
     if (!fits(p.staging_bufs, 4, 3)) {
@@ -1311,7 +1349,9 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
   {
     static int ep_env = -1;
     if (ep_env < 0) { const char* e = getenv("B200SEG_EPI_PRIVATE"); ep_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
-    p.epi_private = (strip && ep_env && p.block_n == 64 && p.n_total == 64 && p.ocb == 64 && p.staging_bufs == 2 &&
+    // fprop: 64-channel layers; dgrad: any strip layer with up to three 64-column groups per tile
+    const bool shape_ok = p.block_n == 64 || (bmn && p.block_n % 64 == 0 && p.block_n <= 192);
+    p.epi_private = (strip && ep_env && shape_ok && p.ocb == 64 && p.staging_bufs == 2 &&
                      p.staging_bytes >= 16384 && kClusterSize == 1) ? 1 : 0;
   }
   if (!strip) {
