@@ -1,9 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-b() { tag=$1; shift; env "$@" timeout 600 python bench.py --steps 20 --warmup 5 --no-e2e > gpurun_out/s_$tag.json 2> gpurun_out/s_$tag.err; python -c "
-import json; d=json.loads(open('gpurun_out/s_$tag.json').read().strip().split('\n')[-1]); print('$tag', d['value'], d['ms_per_step'], d['clocks']['sm_mhz'])"; }
-b new X=1
-b old B200SEG_STRIP_N=256 B200SEG_DGRAD_N64=0
-b new2 X=1
-b oldn B200SEG_STRIP_N=256
-b oldd B200SEG_DGRAD_N64=0
+timeout 600 python -m pytest tests/test_gpu_multi.py -q -x -s -k "overlapped" > gpurun_out/s_multi.log 2>&1; grep -E "passed|failed|comm_ms|Error|assert" gpurun_out/s_multi.log | cut -c1-600 | tail -6

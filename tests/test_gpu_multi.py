@@ -262,6 +262,9 @@ def _overlap_worker(rank, world, port, graph, q, out_dir):
         losses.append(tr.train_epoch()["mean_loss"])
         tr.epoch += 1
     tr.overlap.check_abort()
+    before = tr.model.flat["param"].clone()
+    res["comm"] = tr.calibrate_comm(img, lab, reps=2)          # what fit() logs: comm_ms, comm_exposed_ms, overlap_pct
+    assert torch.equal(before, tr.model.flat["param"]) and float(tr.sync.flat.abs().max()) == 0.0
     chk = tr.model.flat["param"].double().sum().reshape(1)
     lst = [torch.zeros_like(chk) for _ in range(world)]
     dist.all_gather(lst, chk)
@@ -291,6 +294,7 @@ def test_overlapped_exchange_matches_nccl_and_replicas_identical(graph, tmp_path
     for err, scale in res["errs"]:
         assert err <= 2e-4 * scale + 1e-6, res["errs"]       # wgrad accumulation order differs run to run
     assert all(res["same"]), "replicas must hold identical bits after the exchange (R:402-433)"
+    assert set(res["comm"]) == {"comm_ms", "comm_exposed_ms", "overlap_pct"} and res["comm"]["comm_ms"] > 0
     assert res["losses"][-1] < res["losses"][0]
     s = res["param_sums"]
     assert max(s) == min(s), s                                 # bit-identical replicas after training
