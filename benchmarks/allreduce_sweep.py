@@ -42,13 +42,16 @@ def main():
     ap.add_argument("--max-mb", type=int, default=512)
     ap.add_argument("--out", default="")
     ap.add_argument("--grid-sweep", action="store_true", help="also time the NVLS kernel at 32..256 CTAs")
+    ap.add_argument("--min-mb", type=float, default=0.0625)
+    ap.add_argument("--nvls-only", action="store_true")
+    ap.add_argument("--blocks", default="32,64,128,256")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = pdist.DistContext(rank, world, local, torch.device("cuda", local), "nccl", False)
     rows = []
-    size = 64 * 1024
+    size = int(a.min_mb * (1 << 20))
     while size <= a.max_mb << 20:
         n = size // 4
         x = torch.randn(n, device="cuda")
@@ -58,6 +61,8 @@ def main():
         variants = [("twoshot", "fp32"), ("twoshot", "bf16"), ("twoshot", "int8s")]
         if size <= symm.ONESHOT_MAX_BYTES:
             variants.append(("oneshot", "fp32"))
+        if a.nvls_only:
+            variants = []
         probe = symm.SymmetricAllReduce(x, ctx, get_codec("fp32"), algorithm="twoshot")
         if probe.multicast_ptr:
             variants.append(("nvls", "fp32"))
@@ -67,7 +72,7 @@ def main():
                 ar = symm.SymmetricAllReduce(x, ctx, get_codec(codec), algorithm=algo)
                 row[f"{algo}_{codec}_ms"] = timed(lambda: ar.all_reduce_(), 20, world, local)
                 if algo == "nvls" and a.grid_sweep and size >= (16 << 20):
-                    for blocks in (32, 64, 128, 256):      # CTAs of 512 threads, 4 x 16 B in flight per thread
+                    for blocks in [int(b) for b in a.blocks.split(",")]:      # CTAs of 512 threads
                         ar.blocks = blocks
                         row[f"nvls_fp32_b{blocks}_ms"] = timed(lambda: ar.all_reduce_(), 20, world, local)
                 del ar

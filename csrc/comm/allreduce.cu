@@ -216,6 +216,7 @@ namespace b200 {
 // all ranks and return the sum; multimem.st writes the result to all ranks.  Rank r does this for
 // slice r only, so every element is reduced once (one owner => identical bits everywhere) and each
 // GPU moves ~S/W bytes in and S/W out instead of (W-1)/W * S each way.
+template <int U>
 __global__ void __launch_bounds__(kArThreads)
 allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, size_t n_vec, float post_scale,
                       uint32_t epoch, unsigned long long timeout_ns) {
@@ -224,11 +225,11 @@ allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, 
   const size_t v0 = (size_t)rank * per;
   const size_t v1 = v0 + per < n_vec ? v0 + per : n_vec;
   const size_t nthr = (size_t)gridDim.x * blockDim.x;
-  // four independent 16-byte switch reductions in flight per thread before the first store
-  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += 4 * nthr) {
-    float4 v[4];
+  // U independent 16-byte switch reductions in flight per thread before the first store
+  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += U * nthr) {
+    float4 v[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t j = i + (size_t)u * nthr;
       if (j < v1)
         asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
@@ -237,7 +238,7 @@ allreduce_nvls_kernel(PeerPtrs pp, float* __restrict__ mc, int rank, int world, 
                      : "memory");
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t j = i + (size_t)u * nthr;
       if (j < v1) {
         v[u].x *= post_scale; v[u].y *= post_scale; v[u].z *= post_scale; v[u].w *= post_scale;
@@ -507,7 +508,13 @@ extern "C" int b200seg_allreduce_nvls(unsigned int* const* signal_ptrs, float* m
     return (int)cudaErrorInvalidValue;
   PeerPtrs pp{};
   for (int r = 0; r < world; ++r) pp.signal[r] = signal_ptrs[r];
-  allreduce_nvls_kernel<<<blocks, kArThreads, 0, st>>>(pp, multicast_ptr, rank, world, (size_t)n_elems / 4, post_scale,
-                                                      epoch, g_comm_timeout_ns);
+  static int unroll = -1;             // B200SEG_NVLS_UNROLL=4|8: switch reductions in flight per thread
+  if (unroll < 0) { const char* e = getenv("B200SEG_NVLS_UNROLL"); unroll = (e != nullptr && e[0] == '8') ? 8 : 4; }
+  if (unroll == 8)
+    allreduce_nvls_kernel<8><<<blocks, kArThreads, 0, st>>>(pp, multicast_ptr, rank, world, (size_t)n_elems / 4, post_scale,
+                                                           epoch, g_comm_timeout_ns);
+  else
+    allreduce_nvls_kernel<4><<<blocks, kArThreads, 0, st>>>(pp, multicast_ptr, rank, world, (size_t)n_elems / 4, post_scale,
+                                                           epoch, g_comm_timeout_ns);
   return (int)cudaGetLastError();
 }
