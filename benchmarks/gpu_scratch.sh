@@ -1,12 +1,4 @@
 #!/bin/bash
-N=4
 mkdir -p gpurun_out
-for U in 4 8; do
-B200SEG_NVLS_UNROLL=$U timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 benchmarks/allreduce_sweep.py --min-mb 64 --max-mb 256 --nvls-only --grid-sweep --blocks 8,16,32,64 --out gpurun_out/s_nvls_u$U.jsonl > gpurun_out/s_nvls_u$U.log 2>&1
-python - <<PY
-import json
-for l in open('gpurun_out/s_nvls_u$U.jsonl'):
-    r=json.loads(l)
-    print('U=$U', r['bytes']>>20,'MB', {k[:-7]:v for k,v in r.items() if k.endswith('_busGBs')})
-PY
-done
+for i in 1 2 3; do timeout 600 python -m pytest tests/test_gpu_train.py -q -x -k headline -s > gpurun_out/s_t$i.log 2>&1; grep -E "passed|failed|worst|Assertion" gpurun_out/s_t$i.log | cut -c1-250 | tail -3; done
+sort -r gpurun_out/grad_errors_headline_shape.txt | head -5

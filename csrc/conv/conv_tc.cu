@@ -1277,7 +1277,10 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     // the 64 -> 64 layers; as ONE 192-column tile the 216 KB bank is streamed from L2 for every 128 pixels.
     static int dn_env = -1;
     if (dn_env < 0) { const char* e = getenv("B200SEG_DGRAD_N64"); dn_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
-    if (strip && dn_env && mode == 1 && Kc == 64 && p.ocb == 64 && n_total > 64 && n_total <= 256 && (H % 4 == 0))
+    // The same holds for a forward conv with 64 input channels and a wider output (the encoder's 64 -> 128): two
+    // resident 64-column N tiles with register statistics instead of one streamed, epilogue-bound 128-column tile.
+    if (strip && dn_env && (mode == 0 || mode == 1) && Kc == 64 && p.ocb == 64 && n_total > 64 && n_total <= 256 &&
+        (H % 4 == 0))
       p.block_n = 64;
   }
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;

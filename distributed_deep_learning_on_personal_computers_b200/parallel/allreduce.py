@@ -89,6 +89,8 @@ class GradientSynchronizer:
         if world > 1 or self.star is not None:
             if self.backend == "native":
                 self.native.all_reduce_()
+                if self.requantize_output and self.codec.name != "fp32":
+                    self._roundtrip_local()      # the reference quantizes the reduced gradient again (Q6, R:367-387)
             elif self.backend == "star":
                 self._sync_star()
             else:

@@ -63,6 +63,11 @@ class Trainer:
             self._rebind_grad(self.sync.flat)
 
         self.engine_kind = cfg.engine if cfg.engine != "auto" else "native"
+        if self.sync.fused and self.ctx.is_coordinator:
+            import warnings
+            warnings.warn("comm=fused adds weight gradients through the NVSwitch multicast alias: replicas agree to "
+                          "rounding (arrival order differs per replica), not bit for bit, and it measured slower than the "
+                          "default exchange under backward (DESIGN.md section 4)")
         if self.sync.fused and (self.engine_kind != "native" or os.environ.get("B200SEG_CONV", "") == "cudnn"):
             raise ValueError("comm=fused needs the native engine with the tcgen05 wgrad kernels "
                              "(they are what performs the reduction)")

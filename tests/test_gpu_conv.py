@@ -28,6 +28,7 @@ SHAPES = [  # N, H, W, Cin, Cout
     (1, 40, 64, 192, 64),      # wgrad strip ring wraps (mirror slot), two pieces per column
     (2, 40, 128, 64, 256),     # wgrad strip, 128-column variant + tap (2,2) on the split-K kernel
     (2, 8, 128, 192, 64),      # dgrad: three 64-column N tiles, each with its resident bank slice and four-row units
+    (2, 8, 256, 64, 128),      # fprop: two such N tiles (64 -> 128), register statistics per tile
     (1, 8, 256, 128, 256),     # strip mode, 256 output channels as two 128-column N tiles with two-row units
 ]
 
