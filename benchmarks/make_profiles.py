@@ -1,0 +1,102 @@
+#!/usr/bin/env python
+"""Turn the raw outputs of ``benchmarks/gpu_final_1gpu.sh`` (in ``gpurun_out/``) into the committed summaries:
+
+    profiles/conv_layers_b64_n16_512.txt, profiles/conv_layers_b128_n16_512.txt   per-layer tables
+    profiles/step_kernels_own_tcgen05.txt, profiles/step_kernels_reference.txt    per-kernel shares of one step
+    profiles/roofline_summary.txt                                                 fractions of the measured peaks
+    profiles/bench_1gpu_{own,ref}.json                                            the two bench.py lines
+
+    python benchmarks/make_profiles.py
+"""
+import json
+import os
+import re
+import shutil
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
+H = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+
+
+def table(src, dst, title):
+    rows = [json.loads(l) for l in open(os.path.join(G, src))]
+    lines = [f"# {title}",
+             "# CUDA events, 3 warm-up + N timed calls, benchmarks/conv_layers.py; ours = tcgen05 kernels (fprop includes the BN statistics",
+             "# epilogue, no conv bias, as in the engine); cudnn = the torch library call: F.conv2d forward, and ITS autograd backward on",
+             "# channels-last tensors for dgrad / wgrad (round 1 timed conv2d_input on permuted views, a slow cuDNN plan: that comparison is",
+             "# withdrawn).  frac = ours TFLOP/s / measured sustained bf16 rate (MEASURED_PEAKS.json, 1405.9 TFLOP/s; burst 1656).  Isolated",
+             f"# kernels run at burst clocks, so frac can exceed 1.  commit {H}.  Box-to-box spread on this pool is a few per cent.",
+             "layer     op       HW   cin  cout  ours_ms  cudnn_ms  ours_TF   frac  ours/cudnn"]
+    tot = {}
+    for r in rows:
+        lines.append(f"{r['layer']:9s} {r['op']:6s} {r['HW']:4d} {r['cin']:5d} {r['cout']:5d} {r['ours_ms']:8.3f} {r['cudnn_ms']:9.3f} "
+                     f"{r['ours_tflops']:8.1f} {r['ours_frac_of_measured_peak']:6.2f} {r['ours_ms'] / r['cudnn_ms']:8.2f}")
+        t = tot.setdefault(r["op"], [0.0, 0.0])
+        t[0] += r["ours_ms"]
+        t[1] += r["cudnn_ms"]
+    for k, v in tot.items():
+        lines.append(f"# total {k}: ours {v[0]:.2f} ms, cudnn {v[1]:.2f} ms")
+    open(os.path.join(P, dst), "w").write("\n".join(lines) + "\n")
+    return tot
+
+
+def main():
+    t = table("fin_conv_layers_b64.jsonl", "conv_layers_b64_n16_512.txt",
+              "per-layer conv timing, U-Net b=64, batch 16, 512x512 (headline config)")
+    table("fin_conv_layers_b128.jsonl", "conv_layers_b128_n16_512.txt",
+          "per-layer conv timing, U-Net b=128 (BASELINE config 3), batch 16, 512x512")
+    for src, dst in (("fin_step_own.txt", "step_kernels_own_tcgen05.txt"), ("fin_step_ref.txt", "step_kernels_reference.txt")):
+        s = open(os.path.join(G, src)).read()
+        open(os.path.join(P, dst), "w").write(
+            f"# torch.profiler (CUPTI) device times per kernel, averaged per step; commit {H}; own arm: CUDA-graph replays in steady state\n" + s)
+    for arm in ("own", "ref"):
+        shutil.copy(os.path.join(G, f"fin_bench_1_{arm}.json"), os.path.join(P, f"bench_1gpu_{arm}.json"))
+    own = json.loads(open(os.path.join(G, "fin_bench_1_own.json")).read().strip().split("\n")[-1])
+    ref = json.loads(open(os.path.join(G, "fin_bench_1_ref.json")).read().strip().split("\n")[-1])
+    lines = open(os.path.join(P, "step_kernels_own_tcgen05.txt")).read().splitlines()
+    k = {}
+    for l in lines:
+        m = re.match(r"\s+([\d.]+) ms\s+[\d.]+%\s+x\s*([\d.]+)\s+(.*)", l)
+        if m:
+            k[m.group(3)[:60]] = float(m.group(1))
+
+    def tot(*pats):
+        return sum(v for n, v in k.items() if any(p in n for p in pats))
+
+    cf = tot("tap_gemm_kernel<64, false", "tap_gemm_kernel<16, false")
+    cd = tot("tap_gemm_kernel<64, true")
+    cw = tot("wgrad_")
+    conv = cf + cd + cw
+    bnf, bnr, bna = tot("bn_relu_pool_fwd"), tot("bn_bwd_reduce"), tot("bn_bwd_apply")
+    head, adam = tot("head_ce"), tot("fused_adam")
+    out = f"""# Roofline fractions for ONE training step of the headline config (U-Net b=64, batch 16, 512x512, bf16, 1 GPU), round 2 final
+# kernel times: profiles/step_kernels_own_tcgen05.txt (torch.profiler device times of CUDA-graph replays in steady state):
+#   {lines[1].strip()}
+#   bench.py on the same lease: {own['ms_per_step']:.2f} ms/step = {own['value']:.1f} tiles/s (reference arm {ref['ms_per_step']:.2f} ms = {ref['value']:.1f} tiles/s)
+# denominators: MEASURED_PEAKS.json  bf16 1405.9 TFLOP/s sustained (1656.4 burst), HBM copy 6538 GB/s ("of measured")
+# the whole step runs under sw_power_cap (nvidia-smi reasons in every bench.py JSON line), so in-step times are ~10 % above
+# the isolated per-layer times of profiles/conv_layers_b64_n16_512.txt
+class                     kernels                                              work / step        time     achieved        of measured peak   (round 1)
+conv (tensor core)        tap_gemm, wgrad_pair, wgrad_strip, wgrad_kernel       21.7 TFLOP         {conv:5.2f} ms {21.7 / conv * 1000:5.0f} TFLOP/s    {21.7 / conv * 1000 / 1405.9:.2f}               (20.84 ms, 0.74)
+  fprop + convT fwd       tap_gemm<*,false,*>                                   7.24 TFLOP         {cf:5.2f} ms {7.24 / cf * 1000:5.0f} TFLOP/s    {7.24 / cf * 1000 / 1405.9:.2f}               (6.97 ms)
+  dgrad + convT dgrad     tap_gemm<*,true,*>                                    7.2  TFLOP         {cd:5.2f} ms {7.2 / cd * 1000:5.0f} TFLOP/s    {7.2 / cd * 1000 / 1405.9:.2f}               (6.27 ms)
+  wgrad                   wgrad_pair, wgrad_strip<128>, wgrad_kernel<1>, <2>    7.24 TFLOP         {cw:5.2f} ms {7.24 / cw * 1000:5.0f} TFLOP/s    {7.24 / cw * 1000 / 1405.9:.2f}               (7.60 ms)
+BN+ReLU(+pool) forward    bn_relu_pool_fwd<0>, <1>                              8.2 GB             {bnf:5.2f} ms {8.2 / bnf:4.1f} TB/s        {8.2 / bnf * 1000 / 6538:.2f}
+BN backward, reduce       bn_bwd_reduce<0>, <1>                                 8.2 GB             {bnr:5.2f} ms {8.2 / bnr:4.1f} TB/s        {8.2 / bnr * 1000 / 6538:.2f}
+BN backward, apply        bn_bwd_apply<0>, <1>                                  12.3 GB            {bna:5.2f} ms {12.3 / bna:4.1f} TB/s        {12.3 / bna * 1000 / 6538:.2f}
+head + CE + head backward head_ce_fast<6,64>                                    1.07 GB            {head:5.2f} ms {1.07 / head:4.1f} TB/s        {1.07 / head * 1000 / 6538:.2f} (issue / smem bound)
+Adam                      fused_adam                                            1.05 GB            {adam:5.2f} ms {1.05 / adam:4.1f} TB/s        {1.05 / adam * 1000 / 6538:.2f}
+# per-layer conv numbers against the cuDNN library call on the same tensors: profiles/conv_layers_b64_n16_512.txt
+#   fprop (+BN statistics) {t['fprop'][0]:.2f} vs {t['fprop'][1]:.2f} (conv only)   dgrad {t['dgrad'][0]:.2f} vs {t['dgrad'][1]:.2f}   wgrad {t['wgrad'][0]:.2f} vs {t['wgrad'][1]:.2f}  (sum over the 15 distinct layer shapes, ms)
+#   round 1's "dgrad 4.44 vs 14.30" compared against a slow cuDNN plan and is withdrawn; the dgrad baseline is now autograd of F.conv2d.
+# rows that still lose to cuDNN by more than 25 %: L0.dec0 fprop (N = 64 instructions with streamed weights), L2.c0 / L3.c0 fprop and L1.c0
+# dgrad (two K chunks: the filter bank does not stay resident), L3.dec0 and L4 wgrad (split-K, L2-bound), L5.c0 fprop (21 us: launch-sized).
+# what bounds the tensor-core kernels: profiles/umma_cost_model.txt (one UMMA ~ N/2 + 32 cycles) and profiles/ncu_mma_issue.txt.
+"""
+    open(os.path.join(P, "roofline_summary.txt"), "w").write(out)
+    print(out)
+
+
+if __name__ == "__main__":
+    main()
