@@ -53,6 +53,8 @@ def parse():
     p.add_argument("--conv", default=None, help="tcgen05 | cudnn (own arm only)")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--readback", choices=["lagged", "sync"], default="lagged",
+                   help="e2e arm: host picks up step i's loss while step i+1 runs (lagged) or waits for it at once (sync)")
     p.add_argument("--no-overlap", action="store_true", help="exchange after backward (whole buffer) instead of under it")
     p.add_argument("--preset", default=None, choices=sorted(PRESETS),
                    help="BASELINE.json configs: headline (2, default), b128 (3), tile1024 (4), shipped (reference as shipped)")
@@ -107,8 +109,8 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def timed(fn, steps, dist_ctx, torch):
-    """Device time of ``steps`` calls of fn, max over ranks, in ms."""
+def timed(fn, steps, dist_ctx, torch, finish=None):
+    """Device time of ``steps`` calls of fn (then ``finish``, inside the timed region), max over ranks, in ms."""
     import torch.distributed as dist
     if dist_ctx["world"] > 1:
         dist.barrier(device_ids=[dist_ctx["local"]])
@@ -117,6 +119,8 @@ def timed(fn, steps, dist_ctx, torch):
     a.record()
     for i in range(steps):
         fn(i)
+    if finish is not None:
+        finish()
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b)
@@ -236,16 +240,23 @@ def run_own(args, dctx, torch):
     if not args.no_e2e:
         order = [j % n_tiles for j in range(args.batch * (args.steps + max(args.warmup, 3)))]
         it = tr.loader.batches(order)
-        host_loss = torch.zeros(2, dtype=torch.float32).pin_memory()
+        reads = []
 
         def step_e2e(i):
             img, lab = next(it)                      # H2D from pinned memory on the copy stream
-            out = tr.train_step(img, lab)
-            host_loss.copy_(out, non_blocking=False)  # D2H read of the step's loss / accuracy
+            # every step's (loss_sum, correct) is copied to pinned host memory behind its kernels; the host
+            # picks it up one call later, while the next step runs (args.readback sync: wait for it at once)
+            got = tr.train_step_read(img, lab, lag=0 if args.readback == "sync" else 1)
+            if got is not None:
+                reads.append(got)
 
         for i in range(max(args.warmup, 3)):
             step_e2e(i)
-        ms_e2e = timed(step_e2e, args.steps, dctx, torch)
+        tr.flush_reads()
+        reads.clear()
+        # the last step's values are read inside the timed region too (finish runs before the closing event)
+        ms_e2e = timed(step_e2e, args.steps, dctx, torch, finish=lambda: reads.extend(tr.flush_reads()))
+        assert len(reads) == args.steps and all(v[0] == v[0] for v in reads), "a step's result was not read back"
         h2d, d2h = tr.loader.bytes_per_batch, 8
     tr.check_peers()
     extra = {"engine": "native", "conv": os.environ.get("B200SEG_CONV", "tcgen05"),
@@ -254,6 +265,7 @@ def run_own(args, dctx, torch):
                            (("nvls" if tr.overlap.multicast_ptr else "twoshot") + "-bucketed-under-backward"
                             if tr.overlap is not None else tr.sync.native.algorithm)),
              "grad_buckets": (len(tr.overlap.ovl_buckets) if tr.overlap is not None else 0),
+             "e2e_readback": ("every step, picked up one step late" if args.readback == "lagged" else "every step, waited for at once"),
              # every B200SEG_* switch in effect (they select kernel variants; recorded so no run is ambiguous)
              "env": {k: v for k, v in sorted(os.environ.items()) if k.startswith("B200SEG_")}}
     return _result(args, dctx, "own", ms, ms_e2e, clk, launches, h2d, d2h, extra)

@@ -34,7 +34,7 @@ from .parallel import dist as pdist
 from .parallel.allreduce import GradientSynchronizer
 from .utils import checkpoint as ckpt
 from .utils.data import PinnedBatchLoader, RankSampler, TileSet, build_datasets
-from .utils.metrics import DeviceMeter, RunLog, dump_samples
+from .utils.metrics import DeviceMeter, RunLog, StepReadback, dump_samples
 from .utils.timing import PhaseTimer, nvtx_range
 
 
@@ -85,6 +85,7 @@ class Trainer:
             nat.setup_overlap(buckets, timeout_s=cfg.timeout_s)
             self.overlap = nat
         self._reduced = False         # the pending gradients were already all-reduced under backward
+        self._readback: Optional[StepReadback] = None   # pinned ring of train_step_read
         self.comm_stats: Dict[str, float] = {}
         self.optimizer = build_optimizer(self.model, cfg)
         self.optimizer.rebind_grad(self.model.flat["grad"])
@@ -194,6 +195,20 @@ class Trainer:
         self.global_step += 1
         self.sync_and_step()
         return out
+
+    def train_step_read(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, lag: int = 1):
+        """``train_step`` plus a host read of its ``(loss_sum, correct)``, pipelined: this step's 8-byte copy
+        is queued behind its kernels, and the call returns the host values of the step ``lag`` calls ago
+        (``None`` for the first ``lag`` calls), so the host is never waiting on the step it has just
+        launched (the reference's ``.cpu()`` per micro-batch, R:775-776, drains the GPU every time).
+        ``flush_reads()`` returns what is still in flight."""
+        if self._readback is None:
+            self._readback = StepReadback(self.device, depth=max(lag + 1, 2))
+        self._readback.push(self.train_step(images_u8, labels_u8))
+        return self._readback.pop() if self._readback.in_flight() > lag else None
+
+    def flush_reads(self):
+        return [] if self._readback is None else self._readback.drain()
 
     def _micro_step_autograd(self, images_u8, labels_u8) -> torch.Tensor:
         """Stock-PyTorch path (eager autograd, as the reference's R:754-756), for comparison."""

@@ -128,3 +128,49 @@ class DeviceMeter:
     def reset(self) -> None:
         self.acc.zero_()
         self.pixels = 0
+
+
+class StepReadback:
+    """Per-step device-to-host read of ``[loss_sum, correct]`` that never stalls the step it belongs to.
+
+    The reference reads loss and accuracy back with ``.cpu()`` right after every micro-batch (R:775-776):
+    the host then cannot queue the next step until this one has drained, and the GPU idles for the host's
+    launch time at every step.  Here ``push`` queues the 8-byte copy into a pinned ring slot behind the
+    step's kernels and records an event; ``pop`` waits for the OLDEST outstanding slot.  Called as
+    ``push(step i); pop() -> values of step i-1`` the host waits while the GPU is already running step i,
+    so every step's result still reaches the host, one step late."""
+
+    def __init__(self, device: torch.device, depth: int = 4, width: int = 2):
+        self.cuda = device.type == "cuda"
+        self.slots = [torch.zeros(width, dtype=torch.float32, pin_memory=self.cuda) for _ in range(depth)]
+        self.events = [torch.cuda.Event() for _ in range(depth)] if self.cuda else None
+        self.head = self.tail = 0               # tail .. head-1 are in flight
+        self.bytes_per_read = width * 4
+
+    def in_flight(self) -> int:
+        return self.head - self.tail
+
+    def push(self, values: torch.Tensor) -> None:
+        if self.in_flight() == len(self.slots):
+            raise RuntimeError("StepReadback ring is full: pop() before pushing more")
+        k = self.head % len(self.slots)
+        self.slots[k].copy_(values.detach().to(torch.float32), non_blocking=True)
+        if self.cuda:
+            self.events[k].record()
+        self.head += 1
+
+    def pop(self):
+        """Host values of the oldest pushed step (waits for it), or None when nothing is in flight."""
+        if self.in_flight() == 0:
+            return None
+        k = self.tail % len(self.slots)
+        if self.cuda:
+            self.events[k].synchronize()
+        self.tail += 1
+        return tuple(self.slots[k].tolist())
+
+    def drain(self):
+        out = []
+        while self.in_flight():
+            out.append(self.pop())
+        return out

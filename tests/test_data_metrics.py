@@ -58,3 +58,36 @@ def test_cli_defaults_are_the_reference_constants():
     assert cfg.codec == "q201" and cfg.compress and cfg.lr == 1e-3 and cfg.master_port == 5005
     cfg = parse_cli(["--codec", "float16", "--base-channels", "64", "--compress", "false"])
     assert cfg.codec == "q201" and cfg.base_channels == 64 and cfg.compress is False
+
+
+def test_step_readback_returns_every_step_one_late():
+    rb = metrics.StepReadback(torch.device("cpu"), depth=2)
+    assert rb.pop() is None
+    got = []
+    for i in range(5):
+        rb.push(torch.tensor([float(i), 10.0 * i]))
+        if rb.in_flight() > 1:
+            got.append(rb.pop())
+    got += rb.drain()
+    assert got == [(float(i), 10.0 * i) for i in range(5)] and rb.in_flight() == 0
+
+
+def test_train_step_read_matches_train_step(tmp_path):
+    from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
+    mk = lambda: Trainer(TrainConfig(base_channels=8, tile=32, batch_size=2, train_tiles=4, holdout_tiles=0,
+                                     sync_every=1, world_size=1, codec="fp32", device="cpu", sample_images=0,
+                                     out_dir=str(tmp_path), seed=3))
+    a, b = mk(), mk()
+    tiles = data.synthetic_tiles(4, tile=32, seed=1)
+    direct, lagged = [], []
+    for i in range(3):
+        img, lab = tiles.images[(i % 2) * 2:(i % 2) * 2 + 2], tiles.labels[(i % 2) * 2:(i % 2) * 2 + 2]
+        direct.append(tuple(a.train_step(img, lab).tolist()))
+        got = b.train_step_read(img, lab)
+        assert (got is None) == (i == 0)
+        if got is not None:
+            lagged.append(got)
+    lagged += b.flush_reads()
+    assert len(lagged) == 3
+    for x, y in zip(direct, lagged):
+        assert abs(x[0] - y[0]) <= 1e-4 * abs(x[0]) and x[1] == y[1]
