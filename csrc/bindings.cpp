@@ -118,6 +118,50 @@ void head_ce_fwd_bwd(const Tensor& a, const Tensor& w, const Tensor& b, const Te
                      cur()), "head_ce");
 }
 
+// BN(train)+ReLU on load + head + loss + head backward + the BN-backward sums, one pass over the raw conv output
+int64_t head_tail_rows(int64_t P, int64_t C) { return b200seg_head_tail_rows(P, (int)C); }
+bool head_tail_supported(int64_t C, int64_t K) { return b200seg_head_tail_supported((int)C, (int)K) != 0; }
+
+void head_tail_fwd_bwd(const Tensor& y, const Tensor& ss, const Tensor& w, const Tensor& b, const Tensor& labels,
+                       double grad_scale, OptT g_out, OptT dw, OptT db, OptT pred, Tensor loss_acc, OptT bn_partial) {
+  c10::cuda::CUDAGuard g(y.device());
+  bf16(y, "y");
+  const int C = (int)y.size(3), K = (int)w.size(0);
+  const int64_t P = y.size(0) * y.size(1) * y.size(2);
+  TORCH_CHECK(b200seg_head_tail_supported(C, K), "head_tail: unsupported (C, classes) = (", C, ", ", K, ")");
+  TORCH_CHECK(w.size(1) == C && w.is_contiguous(), "head weight must be (classes, C) contiguous");
+  TORCH_CHECK(ss.is_contiguous() && ss.size(0) == 4 && ss.size(1) == C, "ss must be (4, C)");
+  TORCH_CHECK(labels.scalar_type() == at::kByte && labels.is_contiguous() && labels.numel() == P, "labels must be uint8, one per pixel");
+  int64_t ld_g = 0;
+  if (g_out.has_value()) {
+    bf16(*g_out, "g_out");
+    ld_g = nhwc_ld(*g_out, "g_out");
+    TORCH_CHECK(dw.has_value() && db.has_value() && bn_partial.has_value(), "head_tail backward needs dw, db and bn_partial");
+    TORCH_CHECK(bn_partial->is_contiguous() && bn_partial->numel() >= b200seg_head_tail_rows(P, C) * 2 * (int64_t)C,
+                "bn_partial too small");
+  }
+  Tensor& ws = head_workspace(y, b200seg_head_ce_workspace_bytes(C, K));
+  ok(b200seg_head_tail(y.data_ptr(), nhwc_ld(y, "y"), f32(ss), f32(w), f32(b), labels.data_ptr<uint8_t>(), P, C, K,
+                       (float)grad_scale, ptr_or_null(g_out), ld_g, dw.has_value() ? f32(*dw) : nullptr,
+                       db.has_value() ? f32(*db) : nullptr, pred.has_value() ? pred->data_ptr<uint8_t>() : nullptr,
+                       f32(loss_acc), bn_partial.has_value() ? f32(*bn_partial) : nullptr, ws.data_ptr(), cur()),
+     "head_tail");
+}
+
+void bn_relu_bwd_from_partial(const Tensor& partial, int64_t rows, const Tensor& d_out, const Tensor& y, const Tensor& ss,
+                              const Tensor& gamma, Tensor dgamma, Tensor dbeta, Tensor dy) {
+  c10::cuda::CUDAGuard g(y.device());
+  bf16(y, "y"); bf16(dy, "dy"); bf16(d_out, "d_out");
+  const int C = (int)y.size(3);
+  TORCH_CHECK(partial.is_contiguous() && partial.numel() >= rows * 2 * (int64_t)C, "partial too small");
+  auto coef = at::empty({3 * (int64_t)C}, y.options().dtype(at::kFloat));
+  ok(b200seg_bn_relu_bwd_from_partial(f32(partial), (int)rows, d_out.data_ptr(), nhwc_ld(d_out, "d_out"), y.data_ptr(),
+                                      nhwc_ld(y, "y"), f32(ss), f32(gamma), f32(dgamma), f32(dbeta), dy.data_ptr(),
+                                      nhwc_ld(dy, "dy"), (int)y.size(0), (int)y.size(1), (int)y.size(2), C,
+                                      coef.data_ptr<float>(), cur()),
+     "bn_relu_bwd_from_partial");
+}
+
 void fused_adam(Tensor p, Tensor gr, Tensor m, Tensor v, double lr, double b1, double b2, double eps,
                 double wd, double gscale, double bc1, double bc2, OptT p_lowp, bool zero_grad) {
   c10::cuda::CUDAGuard g(p.device());
@@ -402,6 +446,13 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("bn_relu_pool_fwd(Tensor y, Tensor ss, Tensor(a!) out, Tensor(b!)? pool) -> ()", &bn_relu_pool_fwd);
   m.def("bn_relu_pool_bwd(Tensor? d_out, Tensor? d_pool, Tensor y, Tensor ss, Tensor gamma, Tensor(a!) dgamma, "
         "Tensor(b!) dbeta, Tensor? dbias, Tensor(c!) dy) -> ()", &bn_relu_pool_bwd);
+  m.def("head_tail_rows(int P, int C) -> int", &head_tail_rows);
+  m.def("head_tail_supported(int C, int K) -> bool", &head_tail_supported);
+  m.def("head_tail_fwd_bwd(Tensor y, Tensor ss, Tensor w, Tensor b, Tensor labels, float grad_scale, Tensor(a!)? g_out, "
+        "Tensor(b!)? dw, Tensor(c!)? db, Tensor(d!)? pred, Tensor(e!) loss_acc, Tensor(f!)? bn_partial) -> ()",
+        &head_tail_fwd_bwd);
+  m.def("bn_relu_bwd_from_partial(Tensor partial, int rows, Tensor d_out, Tensor y, Tensor ss, Tensor gamma, "
+        "Tensor(a!) dgamma, Tensor(b!) dbeta, Tensor(c!) dy) -> ()", &bn_relu_bwd_from_partial);
   m.def("head_ce_fwd_bwd(Tensor a, Tensor w, Tensor b, Tensor labels, float grad_scale, Tensor(a!)? da, "
         "Tensor(b!)? dw, Tensor(c!)? db, Tensor(d!)? pred, Tensor(e!) loss_acc) -> ()", &head_ce_fwd_bwd);
   m.def("fused_adam(Tensor(a!) p, Tensor(b!) g, Tensor(c!) m, Tensor(d!) v, float lr, float beta1, float beta2, "

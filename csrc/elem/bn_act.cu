@@ -546,3 +546,20 @@ extern "C" int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, cons
   }
   return (int)cudaGetLastError();
 }
+
+// The same backward when the two per-channel sums were already produced by the kernel that wrote d_out
+// (csrc/elem/head_tail.cu for the last stage): finalize + apply only.  partial: float[rows][2][C];
+// coef: float[3*C] scratch.
+extern "C" int b200seg_bn_relu_bwd_from_partial(const float* partial, int rows, const void* d_out, long long ld_do,
+                                                const void* y, long long ld_y, const float* ss, const float* gamma,
+                                                float* dgamma, float* dbeta, void* dy, long long ld_dy, int N, int H,
+                                                int W, int C, float* coef, cudaStream_t st) {
+  if (C % 8 || C > 2048 || rows < 1 || kThreads / (C / 8) < 1) return (int)cudaErrorInvalidValue;
+  const long long P = (long long)N * H * W;
+  launch_k(bn_bwd_finalize_kernel, (C + 3) / 4, 128, 0, st, partial, rows, P, gamma, ss, dgamma, dbeta, coef, C);
+  const int grid = grid_for_groups(P, C / 8);
+  launch_k(bn_bwd_apply_kernel<false>, grid, kThreads, 0, st, (const __nv_bfloat16*)d_out, ld_do,
+           (const __nv_bfloat16*)nullptr, 0ll, (const __nv_bfloat16*)y, ld_y, ss, coef, N, H, W, C, (__nv_bfloat16*)dy,
+           ld_dy);
+  return (int)cudaGetLastError();
+}

@@ -50,7 +50,8 @@ class NativeEngine:
     """Runs forward + loss + backward of one micro-batch over the model's flat buffers."""
 
     def __init__(self, model: UNet, batch: int, height: int, width: int,
-                 act_dtype: Optional[torch.dtype] = None, conv_impl: str = "auto"):
+                 act_dtype: Optional[torch.dtype] = None, conv_impl: str = "auto",
+                 fused_tail: Optional[bool] = None):
         if height % 32 or width % 32:
             raise ValueError("H and W must be multiples of 32 (five 2x2 pools, R:644-648)")
         self.model = model
@@ -62,6 +63,12 @@ class NativeEngine:
         self.conv_impl = conv_impl
         self.N, self.H, self.W = batch, height, width
         self.classes = model.out_classes
+        # One pass over the last conv's raw output does its BN+ReLU, the head with loss and backward, and the
+        # two sums of that BN's backward (csrc/elem/head_tail.cu); the last activation is never materialised.
+        if fused_tail is None:
+            import os
+            fused_tail = os.environ.get("B200SEG_HEAD_TAIL", "1") != "0"
+        self._want_fused_tail = bool(fused_tail)
         self.bilinear = model.up_sample_mode == "bilinear"
         # low-precision copy of the weights that the tensor-core kernels read
         if self.act_dtype == torch.float32:
@@ -175,6 +182,11 @@ class NativeEngine:
             order += [s0, s1]
         self.order = order
         self.head_in, self.d_head_in = below, d_below
+        self.tail = s1                                           # up_conv1's second stage feeds the head
+        self.fused_tail = self._want_fused_tail and Fn.head_tail_supported(s1.y, self.classes)
+        if self.fused_tail:
+            self.tail_rows = Fn.head_tail_rows(s1.y)
+            self.tail_partial = self._new(self.tail_rows, 2, s1.spec.cout, dtype=torch.float32)
         for st in order:
             st.ss = self._new(4, st.spec.cout, dtype=torch.float32)
         self.loss_acc = self._new(2, dtype=torch.float32)       # [loss sum, correct] of last call
@@ -199,17 +211,26 @@ class NativeEngine:
                        self._buffers[bn + ".running_mean"], self._buffers[bn + ".running_var"],
                        self._buffers[bn + ".num_batches_tracked"], st.ss, training=self.training,
                        conv_bias=bias)
+        if self.fused_tail and st is self.tail:
+            return                                   # the head kernel applies this BN+ReLU on load
         Fn.bn_relu_pool_fwd(st.y, st.ss, st.out, st.pool)
 
     def _stage_bwd(self, st: _Stage, need_dx: bool = True, colsum: bool = False):
         """``colsum``: also return the per-CTA column sums of ``dx`` from the dgrad epilogue."""
         sp = st.spec
         bn = sp.bn
-        Fn.bn_relu_pool_bwd(st.d_out, st.d_pool if st.pool is not None else None, st.y, st.ss,
-                            self._seg(self.flat_p, bn + ".weight"),
-                            self._seg(self.flat_g, bn + ".weight"),
-                            self._seg(self.flat_g, bn + ".bias"),
-                            self._seg(self.flat_g, sp.name + ".bias"), st.dy)
+        if self.fused_tail and st is self.tail:
+            # the head kernel left sum g and sum g*y of this stage in tail_partial: finalize + apply only
+            Fn.bn_relu_bwd_from_partial(self.tail_partial, self.tail_rows, st.d_out, st.y, st.ss,
+                                        self._seg(self.flat_p, bn + ".weight"),
+                                        self._seg(self.flat_g, bn + ".weight"),
+                                        self._seg(self.flat_g, bn + ".bias"), st.dy)
+        else:
+            Fn.bn_relu_pool_bwd(st.d_out, st.d_pool if st.pool is not None else None, st.y, st.ss,
+                                self._seg(self.flat_p, bn + ".weight"),
+                                self._seg(self.flat_g, bn + ".weight"),
+                                self._seg(self.flat_g, bn + ".bias"),
+                                self._seg(self.flat_g, sp.name + ".bias"), st.dy)
         dw = self._w3(self.flat_g, sp.name + ".weight")
         if self.stem_pad and sp.name == self.stem:
             # stem_dw is zero on entry (allocated zeroed, re-zeroed by the fold below)
@@ -265,6 +286,17 @@ class NativeEngine:
     def _head(self, with_grad: bool, grad_scale: float) -> None:
         wh = self._seg(self.flat_p, "conv_last.weight").view(self.classes, -1)
         bh = self._seg(self.flat_p, "conv_last.bias")
+        if self.fused_tail:
+            st = self.tail
+            if with_grad:
+                dwh = self._seg(self.flat_g, "conv_last.weight").view(self.classes, -1)
+                dbh = self._seg(self.flat_g, "conv_last.bias")
+                Fn.head_tail_fwd_bwd(st.y, st.ss, wh, bh, self.labels, grad_scale, self.d_head_in, dwh, dbh,
+                                     self.pred, self.loss_acc, self.tail_partial)
+            else:
+                Fn.head_tail_fwd_bwd(st.y, st.ss, wh, bh, self.labels, 0.0, None, None, None, self.pred,
+                                     self.loss_acc, None)
+            return
         if with_grad:
             dwh = self._seg(self.flat_g, "conv_last.weight").view(self.classes, -1)
             dbh = self._seg(self.flat_g, "conv_last.bias")

@@ -239,6 +239,37 @@ def head_ce_fwd_bwd(a, w, b, labels, grad_scale, da, dw, db, pred, loss_acc):
     return loss_acc
 
 
+def head_tail_supported(y, classes: int) -> bool:
+    """Can the last stage's BN+ReLU, the head and that BN's backward sums run as one pass over ``y``?"""
+    if _native(y):
+        return bool(_ops().head_tail_supported(int(y.shape[-1]), int(classes)))
+    return True
+
+
+def head_tail_rows(y) -> int:
+    if _native(y):
+        return int(_ops().head_tail_rows(y.shape[0] * y.shape[1] * y.shape[2], y.shape[3]))
+    return 1
+
+
+def head_tail_fwd_bwd(y, ss, w, b, labels, grad_scale, g_out, dw, db, pred, loss_acc, bn_partial):
+    """BN(train)+ReLU on load + 1x1 head + CE + accuracy + head backward + BN-backward sums (head_tail.cu)."""
+    if _native(y):
+        _ops().head_tail_fwd_bwd(y, ss, w, b, labels, float(grad_scale), g_out, dw, db, pred, loss_acc, bn_partial)
+        _tick()
+        return loss_acc
+    loss_acc.copy_(ref.head_tail_fwd_bwd(y, ss, w, b, labels, grad_scale, g_out, dw, db, pred, bn_partial))
+    return loss_acc
+
+
+def bn_relu_bwd_from_partial(partial, rows, d_out, y, ss, gamma, dgamma, dbeta, dy):
+    if _native(y):
+        _ops().bn_relu_bwd_from_partial(partial, int(rows), d_out, y, ss, gamma, dgamma, dbeta, dy)
+        _tick(2)
+        return
+    ref.bn_relu_bwd_from_partial(partial, rows, d_out, y, ss, gamma, dgamma, dbeta, dy)
+
+
 def fused_adam(p, g, m, v, step, lr, beta1, beta2, eps, weight_decay, grad_scale=1.0,
                p_lowp=None, zero_grad=False):
     if _native(p):

@@ -43,6 +43,17 @@ def sources() -> list:
 
 def build(verbose: bool = False) -> str:
     """Compile every CUDA source for sm_100a and link ``lib/libb200seg.so`` (no GPU needed)."""
+    global _tried, _lib_loaded
+    if _lib_loaded is not None:
+        # cpp_extension.load() also LOADS what it built, and a second copy of the same TORCH_LIBRARY in one process
+        # aborts: with the library already in, compile in a child process and keep running the loaded one.
+        import subprocess
+        import sys
+        code = ("import sys; sys.path.insert(0, %r); "
+                "from distributed_deep_learning_on_personal_computers_b200.ops import loader; "
+                "loader.build(verbose=%r)" % (REPO_DIR, bool(verbose)))
+        subprocess.run([sys.executable, "-c", code], check=True)
+        return LIB_PATH
     from torch.utils import cpp_extension
     os.makedirs(LIB_DIR, exist_ok=True)
     build_dir = os.path.join(REPO_DIR, "build", "b200seg")
@@ -62,8 +73,9 @@ def build(verbose: bool = False) -> str:
     )
     built = os.path.join(build_dir, "b200seg_C.so")
     shutil.copy2(built, LIB_PATH)
-    global _tried, _lib_loaded
-    _tried = _lib_loaded is not None
+    # load() registered torch.ops.b200seg from the build directory's file in THIS process; lib/libb200seg.so is a
+    # copy of it and must not be loaded on top (double registration of a TORCH_LIBRARY aborts the interpreter)
+    _lib_loaded, _tried = built, True
     return LIB_PATH
 
 

@@ -213,6 +213,40 @@ def head_ce_fwd_bwd(a: torch.Tensor, w: torch.Tensor, b: torch.Tensor, labels: t
     return torch.stack([loss_sum.float(), correct.float()])
 
 
+# The tail in one pass (csrc/elem/head_tail.cu): BN+ReLU of the last stage applied on load, the head with its
+# loss and backward, and the two per-channel sums of that BN's backward.  ``bn_partial`` is (rows, 2, C).
+def head_tail_fwd_bwd(y: torch.Tensor, ss: torch.Tensor, w: torch.Tensor, b: torch.Tensor, labels: torch.Tensor,
+                      grad_scale: float, g_out: Optional[torch.Tensor], dw: Optional[torch.Tensor],
+                      db: Optional[torch.Tensor], pred: Optional[torch.Tensor],
+                      bn_partial: Optional[torch.Tensor]) -> torch.Tensor:
+    pre = y.float() * ss[0] + ss[1]
+    a = torch.relu(pre).to(y.dtype)                     # what bn_relu_pool_fwd would have stored
+    out = head_ce_fwd_bwd(a, w, b, labels, grad_scale, g_out, dw, db, pred)
+    if g_out is not None:
+        g = g_out.float() * (pre > 0)
+        bn_partial.zero_()
+        bn_partial[0, 0] = g.sum(dim=(0, 1, 2))
+        bn_partial[0, 1] = (g * y.float()).sum(dim=(0, 1, 2))
+    return out
+
+
+def bn_relu_bwd_from_partial(partial: torch.Tensor, rows: int, d_out: torch.Tensor, y: torch.Tensor,
+                             ss: torch.Tensor, gamma: torch.Tensor, dgamma: torch.Tensor, dbeta: torch.Tensor,
+                             dy: torch.Tensor) -> None:
+    """``bn_relu_pool_bwd`` (no pool) with ``sum g`` and ``sum g*y`` given as per-CTA partial rows."""
+    scale, shift, mean, invstd = ss[0], ss[1], ss[2], ss[3]
+    yf = y.float()
+    g = d_out.float() * ((yf * scale + shift) > 0)
+    m = float(yf.shape[0] * yf.shape[1] * yf.shape[2])
+    sums = partial[:rows].to(torch.float64).sum(dim=0)
+    sum_g = sums[0].float()
+    sum_gx = (invstd.double() * (sums[1] - mean.double() * sums[0])).float()
+    dbeta.add_(sum_g)
+    dgamma.add_(sum_gx)
+    xhat = (yf - mean) * invstd
+    dy.copy_(((gamma.float() * invstd) * (g - sum_g / m - xhat * (sum_gx / m))).to(dy.dtype))
+
+
 # K17/K18: Adam / SGD over the flat buffers (torch.optim semantics, R:704, R:437), optionally
 # also refreshing the bf16 copy of the weights that the conv kernels read.
 def fused_adam(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int,

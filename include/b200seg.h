@@ -32,6 +32,13 @@ int b200seg_bn_relu_pool_bwd(const void* d_out, long long ld_do, const void* d_p
                              float* dgamma, float* dbeta, void* dy, long long ld_dy, int N, int H, int W,
                              int C, int pooled, float* workspace, cudaStream_t st);
 
+/* BN backward of a stage whose two per-channel sums came out of the kernel that produced d_out
+ * (b200seg_head_tail): finalize + apply only.  partial: float[rows][2][C]; coef: float[3*C] scratch. */
+int b200seg_bn_relu_bwd_from_partial(const float* partial, int rows, const void* d_out, long long ld_do,
+                                     const void* y, long long ld_y, const float* ss, const float* gamma,
+                                     float* dgamma, float* dbeta, void* dy, long long ld_dy, int N, int H,
+                                     int W, int C, float* coef, cudaStream_t st);
+
 /* ---- 1x1 head + softmax cross-entropy + accuracy + head backward: R:641, R:703, R:755, R:775 -- */
 long long b200seg_head_ce_workspace_bytes(int C, int K);
 /* workspace: the last 256 bytes hold a CTA counter that must be zero before the first launch. */
@@ -39,6 +46,19 @@ int b200seg_head_ce(const void* a, long long ld_a, const float* w, const float* 
                     const unsigned char* labels, long long P, int C, int K, float grad_scale, void* da,
                     long long ld_da, float* dw, float* db, unsigned char* pred, float* loss_acc,
                     void* workspace, cudaStream_t st);
+
+/* The whole tail in one pass over the last conv's RAW output y: BatchNorm(train)+ReLU (R:583-584) applied
+ * on load, head + loss + accuracy + head backward as b200seg_head_ce, and the two per-channel sums of that
+ * BatchNorm's backward (sum g*[a>0], sum g*[a>0]*y) into bn_partial[rows][2][C], rows =
+ * b200seg_head_tail_rows(P, C).  The activated tensor never reaches HBM; g_out receives d(loss)/d(a).
+ * C in {32, 64, 128}, K <= 8 (b200seg_head_tail_supported).  ss: float[4][C] from b200seg_bn_finalize.
+ * g_out == NULL: forward only (loss, accuracy, pred).  Workspace: as b200seg_head_ce. */
+int b200seg_head_tail_supported(int C, int K);
+int b200seg_head_tail_rows(long long P, int C);
+int b200seg_head_tail(const void* y, long long ld_y, const float* ss, const float* w, const float* bias,
+                      const unsigned char* labels, long long P, int C, int K, float grad_scale, void* g_out,
+                      long long ld_g, float* dw, float* db, unsigned char* pred, float* loss_acc,
+                      float* bn_partial, void* workspace, cudaStream_t st);
 
 /* Same computation with NO workspace argument and no allocation of any kind.  (No counterpart in the
  * reference: it has no device code and no notion of a workspace.)  For callers that must not take

@@ -6,7 +6,7 @@ from distributed_deep_learning_on_personal_computers_b200 import UNet
 from distributed_deep_learning_on_personal_computers_b200.models.engine import NativeEngine
 
 
-def _run(mode, n=2, h=64, w=64, b=8):
+def _run(mode, n=2, h=64, w=64, b=8, fused_tail=False):
     torch.manual_seed(1)
     own = UNet(out_classes=6, base_channels=b, up_sample_mode=mode)
     ref = UNet(out_classes=6, base_channels=b, up_sample_mode=mode)
@@ -14,7 +14,8 @@ def _run(mode, n=2, h=64, w=64, b=8):
     own.flatten_parameters()
     img = torch.randint(0, 256, (n, h, w, 3), dtype=torch.uint8)
     lab = torch.randint(0, 6, (n, h, w), dtype=torch.uint8)
-    eng = NativeEngine(own, n, h, w)
+    eng = NativeEngine(own, n, h, w, fused_tail=fused_tail)
+    assert eng.fused_tail == fused_tail
     eng.load_batch(img, lab)
     out = eng.train_microbatch().clone()
     x = (img.float() / 255).permute(0, 3, 1, 2).contiguous()
@@ -24,9 +25,10 @@ def _run(mode, n=2, h=64, w=64, b=8):
     return own, ref, eng, out, logits, loss, lab
 
 
+@pytest.mark.parametrize("fused_tail", [False, True])     # True: last BN+ReLU, head and BN-backward sums as one op
 @pytest.mark.parametrize("mode", ["conv_transpose", "bilinear"])
-def test_engine_matches_autograd(mode):
-    own, ref, eng, out, logits, loss, lab = _run(mode)
+def test_engine_matches_autograd(mode, fused_tail):
+    own, ref, eng, out, logits, loss, lab = _run(mode, fused_tail=fused_tail)
     px = lab.numel()
     assert abs(out[0].item() / px - loss.item()) < 1e-5
     assert out[1].item() == (logits.argmax(1) == lab.long()).sum().item()
@@ -47,8 +49,9 @@ def test_gradients_accumulate_across_microbatches():
     torch.testing.assert_close(own.flat["grad"], 2 * g1, rtol=1e-4, atol=1e-7)
 
 
-def test_eval_uses_running_statistics():
-    own, ref, eng, *_ = _run("conv_transpose")
+@pytest.mark.parametrize("fused_tail", [False, True])
+def test_eval_uses_running_statistics(fused_tail):
+    own, ref, eng, *_ = _run("conv_transpose", fused_tail=fused_tail)
     ref.eval()
     img = torch.randint(0, 256, (2, 64, 64, 3), dtype=torch.uint8)
     lab = torch.randint(0, 6, (2, 64, 64), dtype=torch.uint8)

@@ -107,6 +107,68 @@ def test_head_ce_fwd_bwd(C, K):
     torch.testing.assert_close(acc2.cpu()[0], acc_r[0], rtol=1e-4, atol=1e-2)
 
 
+@pytest.mark.parametrize("C,K,shape", [(64, 6, (2, 24, 20)), (32, 6, (1, 7, 9)), (128, 3, (2, 16, 16)),
+                                       (64, 8, (1, 40, 33)), (128, 7, (1, 9, 11)), (64, 1, (1, 8, 8))])
+def test_head_tail_one_pass(C, K, shape):
+    """BN+ReLU on load + head + CE + head backward + BN-backward sums (csrc/elem/head_tail.cu) against the plain
+    PyTorch fp32 restatement of the same chain (ops.reference.head_tail_fwd_bwd)."""
+    torch.manual_seed(5)
+    N, H, W = shape
+    P = N * H * W
+    assert Fn.head_tail_supported(torch.empty(1, 1, 1, C, device=DEV, dtype=torch.bfloat16), K)
+    y = _bf(torch.randn(N, H, W, C, device=DEV) * 1.5)
+    ss = torch.stack([torch.rand(C) + 0.5, torch.randn(C) * 0.3, torch.randn(C) * 0.1, torch.rand(C) + 0.5]).to(DEV)
+    w = torch.randn(K, C, device=DEV) * 0.2
+    b = torch.randn(K, device=DEV) * 0.1
+    lab = torch.randint(0, K, (N, H, W), dtype=torch.uint8, device=DEV)
+    rows = Fn.head_tail_rows(y)
+    scale = 1.0 / P
+    g_r = torch.empty(N, H, W, C)
+    dw_r, db_r = torch.zeros(K, C), torch.zeros(K)
+    pred_r = torch.empty(N, H, W, dtype=torch.uint8)
+    part_r = torch.zeros(1, 2, C)
+    acc_r = ref.head_tail_fwd_bwd(y.cpu(), ss.cpu(), w.cpu(), b.cpu(), lab.cpu(), scale, g_r, dw_r, db_r, pred_r, part_r)
+    for rep in range(2):                                  # second call: counter reset, accumulation into dw / db
+        g = torch.full_like(y, float("nan"))
+        dw, db = torch.zeros(K, C, device=DEV), torch.zeros(K, device=DEV)
+        pred = torch.full((N, H, W), 255, dtype=torch.uint8, device=DEV)
+        acc = torch.zeros(2, device=DEV)
+        part = torch.full((rows, 2, C), float("nan"), device=DEV)
+        Fn.head_tail_fwd_bwd(y, ss, w, b, lab, scale, g, dw, db, pred, acc, part)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(acc.cpu()[0], acc_r[0], rtol=1e-4, atol=1e-2)
+        assert abs(acc.cpu()[1].item() - acc_r[1].item()) <= 2
+        assert (pred.cpu() != pred_r).float().mean().item() < 2e-3
+        gc = g.cpu().float()
+        assert torch.isfinite(gc).all()
+        assert (gc - g_r).abs().max().item() <= 1.5e-2 * g_r.abs().max().item() + 1e-9
+        torch.testing.assert_close(dw.cpu(), dw_r, rtol=2e-3, atol=2e-3 * dw_r.abs().max().item())
+        torch.testing.assert_close(db.cpu(), db_r, rtol=1e-3, atol=1e-6)
+        # the BatchNorm-backward sums must be those of the g the kernel STORED (bf16) under the mask of y
+        pre = y.cpu().float() * ss.cpu()[0] + ss.cpu()[1]
+        gm = gc * (pre > 0)
+        want = torch.stack([gm.sum(dim=(0, 1, 2)), (gm * y.cpu().float()).sum(dim=(0, 1, 2))])
+        got = part.cpu().double().sum(dim=0).float()
+        assert torch.isfinite(got).all()
+        tol = 1e-3 * torch.stack([gm.abs().sum(dim=(0, 1, 2)), (gm * y.cpu().float()).abs().sum(dim=(0, 1, 2))]) + 1e-9
+        assert ((got - want).abs() <= tol).all()
+    acc2 = torch.zeros(2, device=DEV)
+    pred2 = torch.empty(N, H, W, dtype=torch.uint8, device=DEV)
+    Fn.head_tail_fwd_bwd(y, ss, w, b, lab, 0.0, None, None, None, pred2, acc2, None)      # forward-only form
+    torch.testing.assert_close(acc2.cpu()[0], acc_r[0], rtol=1e-4, atol=1e-2)
+    assert torch.equal(pred2, pred)
+    # finalize + apply from these partial sums == the three-kernel BN backward on the same g
+    gamma = (torch.rand(C, device=DEV) + 0.5)
+    dy_a, dy_b = torch.empty_like(y), torch.empty_like(y)
+    dg_a, dbt_a = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    dg_b, dbt_b = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    Fn.bn_relu_bwd_from_partial(part, rows, g, y, ss, gamma, dg_a, dbt_a, dy_a)
+    Fn.bn_relu_pool_bwd(g, None, y, ss, gamma, dg_b, dbt_b, None, dy_b)
+    torch.testing.assert_close(dg_a, dg_b, rtol=1e-3, atol=1e-4 * dg_b.abs().max().item() + 1e-7)
+    torch.testing.assert_close(dbt_a, dbt_b, rtol=1e-3, atol=1e-4 * dbt_b.abs().max().item() + 1e-7)
+    assert (dy_a.float() - dy_b.float()).abs().max().item() <= 1e-2 * dy_b.float().abs().max().item() + 1e-9
+
+
 def test_fused_adam_matches_torch_adam():
     torch.manual_seed(3)
     n = 64 * 1000

@@ -9,8 +9,8 @@ from distributed_deep_learning_on_personal_computers_b200.trainer import Trainer
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("conv", ["cudnn", "tcgen05"])
-def test_engine_gradients_match_oracle(conv):
+@pytest.mark.parametrize("conv,tail", [("cudnn", False), ("tcgen05", False), ("tcgen05", True)])
+def test_engine_gradients_match_oracle(conv, tail):
     """GPU engine (sm_100a kernels) vs the SAME plan run by the plain-PyTorch oracles on the CPU with
     bf16 storage between ops (identical rounding points), and vs fp32 eager autograd (sanity)."""
     torch.manual_seed(0)
@@ -24,10 +24,11 @@ def test_engine_gradients_match_oracle(conv):
     N, H, W = 4, 128, 128
     img = torch.randint(0, 256, (N, H, W, 3), dtype=torch.uint8, device="cuda")
     lab = torch.randint(0, 6, (N, H, W), dtype=torch.uint8, device="cuda")
-    eng = NativeEngine(own, N, H, W, conv_impl=conv)
+    eng = NativeEngine(own, N, H, W, conv_impl=conv, fused_tail=tail)   # tail: head_tail.cu instead of three kernels
+    assert eng.fused_tail == tail
     eng.load_batch(img, lab)
     out = eng.train_microbatch().clone()
-    eng_cpu = NativeEngine(cpu, N, H, W, act_dtype=torch.bfloat16)
+    eng_cpu = NativeEngine(cpu, N, H, W, act_dtype=torch.bfloat16, fused_tail=False)
     eng_cpu.load_batch(img.cpu(), lab.cpu())
     out_cpu = eng_cpu.train_microbatch().clone()
     assert abs(out[0].item() - out_cpu[0].item()) / out_cpu[0].item() < 2e-2
@@ -47,7 +48,7 @@ def test_engine_gradients_match_oracle(conv):
         assert cos > 0.85, (n, cos)
     import os
     os.makedirs("gpurun_out", exist_ok=True)
-    open(f"gpurun_out/grad_cosines_{conv}.txt", "w").write("\n".join(table) + "\n")
+    open(f"gpurun_out/grad_cosines_{conv}{'_tail' if tail else ''}.txt", "w").write("\n".join(table) + "\n")
     print("worst cosine vs bf16 oracle", worst)
     x = (img.float() / 255).permute(0, 3, 1, 2)
     logits = ref(x)
