@@ -9,3 +9,5 @@ python benchmarks/profile_step.py --impl own --graph --steps 10 --out gpurun_out
 python benchmarks/profile_step.py --impl reference --steps 5 --out gpurun_out/fin_step_ref.txt > /dev/null 2>&1; head -1 gpurun_out/fin_step_ref.txt
 timeout 600 python bench.py --impl reference > gpurun_out/fin_bench_1_ref.json 2> gpurun_out/fin_bench_1_ref.err; cut -c1-150 gpurun_out/fin_bench_1_ref.json
 timeout 600 python bench.py > gpurun_out/fin_bench_1_own.json 2> gpurun_out/fin_bench_1_own.err; cut -c1-150 gpurun_out/fin_bench_1_own.json
+timeout 200 python benchmarks/tail_bench.py > gpurun_out/fin_tail_bench.json 2> gpurun_out/fin_tail_bench.err; cat gpurun_out/fin_tail_bench.json
+B200SEG_HEAD_TAIL=0 timeout 600 python bench.py > gpurun_out/fin_bench_1_own_notail.json 2> gpurun_out/fin_bench_1_own_notail.err; cut -c1-150 gpurun_out/fin_bench_1_own_notail.json

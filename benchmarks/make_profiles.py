@@ -69,11 +69,17 @@ def main():
     cw = tot("wgrad_")
     conv = cf + cd + cw
     bnf, bnr, bna = tot("bn_relu_pool_fwd"), tot("bn_bwd_reduce"), tot("bn_bwd_apply")
-    head, adam = tot("head_ce"), tot("fused_adam")
+    head, adam = tot("head_ce", "head_tail"), tot("fused_adam")
+    notail = None
+    f = os.path.join(G, "fin_bench_1_own_notail.json")
+    if os.path.exists(f):
+        shutil.copy(f, os.path.join(P, "bench_1gpu_own_notail.json"))
+        notail = json.loads(open(f).read().strip().split("\n")[-1])
     out = f"""# Roofline fractions for ONE training step of the headline config (U-Net b=64, batch 16, 512x512, bf16, 1 GPU), round 2 final
 # kernel times: profiles/step_kernels_own_tcgen05.txt (torch.profiler device times of CUDA-graph replays in steady state):
 #   {lines[1].strip()}
-#   bench.py on the same lease: {own['ms_per_step']:.2f} ms/step = {own['value']:.1f} tiles/s (reference arm {ref['ms_per_step']:.2f} ms = {ref['value']:.1f} tiles/s)
+#   bench.py on the same lease: {own['ms_per_step']:.2f} ms/step = {own['value']:.1f} tiles/s (reference arm {ref['ms_per_step']:.2f} ms = {ref['value']:.1f} tiles/s{'' if notail is None else f"; own arm with B200SEG_HEAD_TAIL=0: {notail['ms_per_step']:.2f} ms = {notail['value']:.1f}"})
+#   end to end (H2D of every step's tiles + every step's loss read back): {own['e2e']['value']:.1f} vs {ref['e2e']['value']:.1f} tiles/s
 # denominators: MEASURED_PEAKS.json  bf16 1405.9 TFLOP/s sustained (1656.4 burst), HBM copy 6538 GB/s ("of measured")
 # the whole step runs under sw_power_cap (nvidia-smi reasons in every bench.py JSON line), so in-step times are ~10 % above
 # the isolated per-layer times of profiles/conv_layers_b64_n16_512.txt
@@ -82,10 +88,11 @@ conv (tensor core)        tap_gemm, wgrad_pair, wgrad_strip, wgrad_kernel       
   fprop + convT fwd       tap_gemm<*,false,*>                                   7.24 TFLOP         {cf:5.2f} ms {7.24 / cf * 1000:5.0f} TFLOP/s    {7.24 / cf * 1000 / 1405.9:.2f}               (6.97 ms)
   dgrad + convT dgrad     tap_gemm<*,true,*>                                    7.2  TFLOP         {cd:5.2f} ms {7.2 / cd * 1000:5.0f} TFLOP/s    {7.2 / cd * 1000 / 1405.9:.2f}               (6.27 ms)
   wgrad                   wgrad_pair, wgrad_strip<128>, wgrad_kernel<1>, <2>    7.24 TFLOP         {cw:5.2f} ms {7.24 / cw * 1000:5.0f} TFLOP/s    {7.24 / cw * 1000 / 1405.9:.2f}               (7.60 ms)
-BN+ReLU(+pool) forward    bn_relu_pool_fwd<0>, <1>                              8.2 GB             {bnf:5.2f} ms {8.2 / bnf:4.1f} TB/s        {8.2 / bnf * 1000 / 6538:.2f}
-BN backward, reduce       bn_bwd_reduce<0>, <1>                                 8.2 GB             {bnr:5.2f} ms {8.2 / bnr:4.1f} TB/s        {8.2 / bnr * 1000 / 6538:.2f}
+BN+ReLU(+pool) forward    bn_relu_pool_fwd<0>, <1>  (21 of 22 stages)           7.1 GB             {bnf:5.2f} ms {7.1 / bnf:4.1f} TB/s        {7.1 / bnf * 1000 / 6538:.2f}
+BN backward, reduce       bn_bwd_reduce<0>, <1>     (21 of 22 stages)           7.1 GB             {bnr:5.2f} ms {7.1 / bnr:4.1f} TB/s        {7.1 / bnr * 1000 / 6538:.2f}
 BN backward, apply        bn_bwd_apply<0>, <1>                                  12.3 GB            {bna:5.2f} ms {12.3 / bna:4.1f} TB/s        {12.3 / bna * 1000 / 6538:.2f}
-head + CE + head backward head_ce_fast<6,64>                                    1.07 GB            {head:5.2f} ms {1.07 / head:4.1f} TB/s        {1.07 / head * 1000 / 6538:.2f} (issue / smem bound)
+tail: BN+ReLU + head + CE head_tail<64>  (mma.sync bf16, profiles/tail_kernel.txt) 1.07 GB          {head:5.2f} ms {1.07 / head:4.1f} TB/s        {1.07 / head * 1000 / 6538:.2f} (issue bound; round 1 head alone: 0.50 ms)
+  + head backward + BN-backward sums of the last stage
 Adam                      fused_adam                                            1.05 GB            {adam:5.2f} ms {1.05 / adam:4.1f} TB/s        {1.05 / adam * 1000 / 6538:.2f}
 # per-layer conv numbers against the cuDNN library call on the same tensors: profiles/conv_layers_b64_n16_512.txt
 #   fprop (+BN statistics) {t['fprop'][0]:.2f} vs {t['fprop'][1]:.2f} (conv only)   dgrad {t['dgrad'][0]:.2f} vs {t['dgrad'][1]:.2f}   wgrad {t['wgrad'][0]:.2f} vs {t['wgrad'][1]:.2f}  (sum over the 15 distinct layer shapes, ms)
