@@ -101,8 +101,14 @@ class Trainer:
         self.global_step = 0          # micro-batches seen
         self.pending = 0              # micro-batches accumulated since the last exchange
         self._graphs = {}             # (reduce under backward?) -> (CUDAGraph, launches)
+        self.resumed_from: Optional[str] = None
         if cfg.resume:
-            self.resume(cfg.resume)
+            # "auto": the newest of <out_dir>/checkpoint.pt and <out_dir>/abort.pt if there is one, else a fresh start --
+            # what a supervised job (torchrun --max-restarts N ... --resume auto) needs after PeerLost took it down
+            path = ckpt.latest(cfg.out_dir) if cfg.resume == "auto" else cfg.resume
+            if path:
+                self.resume(path)
+                self.resumed_from = path
 
     # -- plumbing ----------------------------------------------------------------------------------
     def _rebind_grad(self, new_flat: torch.Tensor) -> None:
@@ -398,7 +404,7 @@ class Trainer:
 
     def fit(self) -> Dict[str, float]:
         cfg = self.cfg
-        self.log.header(count_parameters(self.model), resumed=bool(cfg.resume))
+        self.log.header(count_parameters(self.model), resumed=self.resumed_from is not None)
         last: Dict[str, float] = {}
         if self.sync.native is not None and len(self.train_set) >= cfg.batch_size:
             b = cfg.batch_size

@@ -33,6 +33,13 @@ def save(path: str, model, optimizer, epoch: int, step: int, config: Dict,
     return path
 
 
+def latest(out_dir: str, names=("checkpoint.pt", "abort.pt")) -> Optional[str]:
+    """The most recently written checkpoint of a run directory (the per-epoch one or the one rank 0 leaves when a
+    peer is lost), or None."""
+    found = [os.path.join(out_dir, n) for n in names if os.path.isfile(os.path.join(out_dir, n))]
+    return max(found, key=os.path.getmtime) if found else None
+
+
 def load(path: str, model, optimizer=None, map_location="cpu", trusted: bool = False) -> Dict:
     """``trusted=False`` (default) uses torch's restricted unpickler: a checkpoint holds only tensors, dicts,
     lists, tuples and scalars, so nothing else needs to be constructible from the file (the star transport

@@ -62,3 +62,20 @@ def test_torch_engine_matches_native_engine_on_cpu(tmp_path):
     b = Trainer(_cfg(str(tmp_path / "b"), engine="torch"))
     sa, sb = a.train_epoch(), b.train_epoch()
     assert abs(sa["mean_loss"] - sb["mean_loss"]) < 1e-3
+
+
+def test_resume_auto_picks_the_newest_checkpoint_or_starts_fresh(tmp_path):
+    d = str(tmp_path / "run")
+    fresh = Trainer(_cfg(d, resume="auto"))                  # nothing there yet: a fresh start, not an error
+    assert fresh.resumed_from is None and fresh.epoch == 0
+    fresh.fit()                                              # one epoch -> <out_dir>/checkpoint.pt
+    again = Trainer(_cfg(d, resume="auto", epochs=2))
+    assert again.resumed_from.endswith("checkpoint.pt") and again.epoch == 1
+    assert torch.equal(again.model.flat["param"], fresh.model.flat["param"])
+    import os, time
+    time.sleep(0.05)
+    again.train_epoch()
+    again.save(os.path.join(d, "abort.pt"))                  # what Trainer.check_peers leaves behind on PeerLost
+    third = Trainer(_cfg(d, resume="auto", epochs=3))
+    assert third.resumed_from.endswith("abort.pt")
+    assert torch.equal(third.model.flat["param"], again.model.flat["param"])
