@@ -5,6 +5,7 @@
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <optional>
+#include <vector>
 #include <string>
 #include <map>
 #include "b200seg.h"
@@ -160,6 +161,14 @@ void bn_relu_bwd_from_partial(const Tensor& partial, int64_t rows, const Tensor&
                                       nhwc_ld(dy, "dy"), (int)y.size(0), (int)y.size(1), (int)y.size(2), C,
                                       coef.data_ptr<float>(), cur()),
      "bn_relu_bwd_from_partial");
+}
+
+// host-only: which kernel variant / tiling a conv of this shape takes (see B200ConvPlan in b200seg.h)
+std::vector<int64_t> conv_plan(int64_t op, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout) {
+  B200ConvPlan q{};
+  ok(b200conv_plan((int)op, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, &q), "conv_plan");
+  return {q.kernel, q.block_k, q.block_n, q.n_tiles, q.ocb, q.rows_per_unit, q.weights_resident, q.private_epilogue,
+          q.staging_bufs, q.strip_slots, q.stages, q.grid, q.cluster, q.m_tiles, q.smem_bytes};
 }
 
 void fused_adam(Tensor p, Tensor gr, Tensor m, Tensor v, double lr, double b1, double b2, double eps,
@@ -446,6 +455,7 @@ TORCH_LIBRARY(b200seg, m) {
   m.def("bn_relu_pool_fwd(Tensor y, Tensor ss, Tensor(a!) out, Tensor(b!)? pool) -> ()", &bn_relu_pool_fwd);
   m.def("bn_relu_pool_bwd(Tensor? d_out, Tensor? d_pool, Tensor y, Tensor ss, Tensor gamma, Tensor(a!) dgamma, "
         "Tensor(b!) dbeta, Tensor? dbias, Tensor(c!) dy) -> ()", &bn_relu_pool_bwd);
+  m.def("conv_plan(int op, int N, int H, int W, int Cin, int Cout) -> int[]", &conv_plan);
   m.def("head_tail_rows(int P, int C) -> int", &head_tail_rows);
   m.def("head_tail_supported(int C, int K) -> bool", &head_tail_supported);
   m.def("head_tail_fwd_bwd(Tensor y, Tensor ss, Tensor w, Tensor b, Tensor labels, float grad_scale, Tensor(a!)? g_out, "

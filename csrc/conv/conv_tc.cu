@@ -1242,6 +1242,9 @@ static int strip_mode_env() {          // B200SEG_CONV_STRIP=0 disables the stri
 }
 
 // mode: 0 fprop, 1 dgrad, 2 convT forward, 3 convT data gradient
+// What run_tap_gemm decided for the last call of this thread (b200conv_plan reads it after a dry run).
+static thread_local B200ConvPlan g_last_plan;
+
 static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, const float* bias, void* out,
                         long long ld_o, int N, int H, int W, int Kc, int n_total, int conv_cin, float* partials,
                         int* stat_rows_out, bool dry, cudaStream_t st) {
@@ -1387,6 +1390,18 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
                                     : (long long)((p.m_tiles + p.cluster - 1) / p.cluster) * unit;
   if (total < grid) grid = (int)total;
   if (stat_rows_out) *stat_rows_out = grid / p.n_tiles;
+  const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.xslots * p.xslot_bytes +
+                      (size_t)p.staging_bufs * p.staging_bytes + 1024;
+  {
+    B200ConvPlan& q = g_last_plan;
+    q.kernel = strip ? 1 : 0;
+    q.block_k = BK; q.block_n = p.block_n; q.n_tiles = p.n_tiles; q.ocb = p.ocb;
+    q.rows_per_unit = p.rows4 ? 4 : (p.rows2 ? 2 : 1);
+    q.weights_resident = p.b_resident; q.private_epilogue = p.epi_private;
+    q.staging_bufs = p.staging_bufs; q.strip_slots = p.xslots; q.stages = p.stages;
+    q.grid = grid; q.cluster = p.cluster; q.m_tiles = p.m_tiles;
+    q.smem_bytes = (long long)smem;
+  }
   if (dry) return 0;
 
   CUtensorMap ma, mb, mo;
@@ -1434,8 +1449,6 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
     int box[4] = {32, 32, 1, 1};
     if (!make_map(&mo2, out, 4, dims, str, box, 0)) return (int)cudaErrorInvalidValue;
   }
-  const size_t smem = (size_t)p.stages * p.stage_bytes + (size_t)p.xslots * p.xslot_bytes +
-                      (size_t)p.staging_bufs * p.staging_bytes + 1024;
   if (strip) {
     if (BK == 16) return launch_tap<16, false, true>(ma, mb, mo, mo2, p, grid, smem, st);
     if (bmn) return launch_tap<64, true, true>(ma, mb, mo, mo2, p, grid, smem, st);
@@ -1630,8 +1643,8 @@ extern "C" int b200conv_wgrad_taps(const void* x, long long ld_x, const void* dy
 
 // Dispatch: halo-strip kernel (wgrad_strip.cu) when the rows are at least 64 pixels wide, else the
 // split-K kernel above.  B200SEG_WGRAD_KERNEL=splitk|strip forces one of them (for benchmarking).
-extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
-                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+// 0: split-K kernel (this file), 1: 128-column strip kernel + tap (2,2) pass, 2: row-pair kernel
+static int wgrad_kernel_for(int N, int H, int W, int Cin, int Cout) {
   static int force = -1;
   if (force < 0) {
     const char* e = getenv("B200SEG_WGRAD_KERNEL");
@@ -1644,12 +1657,36 @@ extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, lon
   // Measured per layer (profiles/conv_layers_b64_n16_512.txt): the row-pair kernel beats the 128-column strip
   // kernel + its separate tap-(2,2) pass and the split-K kernel wherever rows are >= 64 pixels wide, except
   // for the widest inputs (Cin > 512), where re-reading x once per 64-channel output tile costs more.
-  if (force == 0 && !pair_off && b200conv_wgrad_pair_supported(N, H, W, Cin, Cout) && (pair_all || Cin <= 512))
-    return b200conv_wgrad_pair(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+  if (force == 0 && !pair_off && b200conv_wgrad_pair_supported(N, H, W, Cin, Cout) && (pair_all || Cin <= 512)) return 2;
   const bool strip_ok = (force == 2) ? b200conv_wgrad_strip_supported(N, H, W, Cin, Cout) != 0
                                      : b200conv_wgrad_strip_preferred(N, H, W, Cin, Cout) != 0;
-  if (strip_ok && force != 1) return b200conv_wgrad_strip(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+  return (strip_ok && force != 1) ? 1 : 0;
+}
+
+extern "C" int b200conv_wgrad(const void* x, long long ld_x, const void* dy, long long ld_dy, float* dw, int N,
+                              int H, int W, int Cin, int Cout, cudaStream_t st) {
+  const int k = wgrad_kernel_for(N, H, W, Cin, Cout);
+  if (k == 2) return b200conv_wgrad_pair(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+  if (k == 1) return b200conv_wgrad_strip(x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
   return run_wgrad(0, x, ld_x, dy, ld_dy, dw, N, H, W, Cin, Cout, st);
+}
+
+// Which kernel variant and tiling a conv call of this shape takes, without launching anything (no GPU needed).
+// op: 0 fprop, 1 dgrad, 2 wgrad, 3 transposed-conv forward, 4 transposed-conv dgrad.
+extern "C" int b200conv_plan(int op, int N, int H, int W, int Cin, int Cout, B200ConvPlan* out) {
+  if (out == nullptr) return (int)cudaErrorInvalidValue;
+  *out = B200ConvPlan{};
+  int e = 0;
+  switch (op) {
+    case 0: e = run_tap_gemm(0, nullptr, Cin, nullptr, nullptr, nullptr, Cout, N, H, W, Cin, Cout, Cin, nullptr, nullptr, true, 0); break;
+    case 1: e = run_tap_gemm(1, nullptr, Cout, nullptr, nullptr, nullptr, Cin, N, H, W, Cout, Cin, Cin, nullptr, nullptr, true, 0); break;
+    case 2: out->kernel = 2 + wgrad_kernel_for(N, H, W, Cin, Cout); return 0;
+    case 3: e = run_tap_gemm(2, nullptr, Cin, nullptr, nullptr, nullptr, Cout, N, H, W, Cin, 4 * Cout, Cin, nullptr, nullptr, true, 0); break;
+    case 4: e = run_tap_gemm(3, nullptr, Cout, nullptr, nullptr, nullptr, Cin, N, H, W, Cout, Cin, Cin, nullptr, nullptr, true, 0); break;
+    default: return (int)cudaErrorInvalidValue;
+  }
+  if (e == 0) *out = g_last_plan;
+  return e;
 }
 
 // Backward of ConvTranspose2d(k=2, s=2): d_up is (N, 2h, 2w, Cout) (a channel slice of the concat

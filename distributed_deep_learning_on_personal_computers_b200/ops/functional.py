@@ -239,6 +239,24 @@ def head_ce_fwd_bwd(a, w, b, labels, grad_scale, da, dw, db, pred, loss_acc):
     return loss_acc
 
 
+_PLAN_OPS = {"fprop": 0, "dgrad": 1, "wgrad": 2, "convT_fwd": 3, "convT_dgrad": 4}
+_PLAN_FIELDS = ("kernel", "block_k", "block_n", "n_tiles", "ocb", "rows_per_unit", "weights_resident", "private_epilogue",
+                "staging_bufs", "strip_slots", "stages", "grid", "cluster", "m_tiles", "smem_bytes")
+_PLAN_KERNELS = {0: "tap_gemm/box", 1: "tap_gemm/strip", 2: "wgrad/split-k", 3: "wgrad/strip128", 4: "wgrad/row-pair"}
+
+
+def conv_plan(op: str, n: int, h: int, w: int, cin: int, cout: int) -> dict:
+    """Which tcgen05 kernel variant and tiling a conv of this shape takes (``B200ConvPlan`` in include/b200seg.h).
+    Host-only: works without a GPU once the library is built; honours the ``B200SEG_*`` switches in effect."""
+    from . import loader
+    if loader.library() is None:
+        raise RuntimeError(f"native library not available: {loader.load_error()}")
+    vals = list(_ops().conv_plan(_PLAN_OPS[op], n, h, w, cin, cout))
+    plan = dict(zip(_PLAN_FIELDS, vals))
+    plan["kernel"] = _PLAN_KERNELS[plan["kernel"]]
+    return plan
+
+
 def head_tail_supported(y, classes: int) -> bool:
     """Can the last stage's BN+ReLU, the head and that BN's backward sums run as one pass over ``y``?"""
     if _native(y):

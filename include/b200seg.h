@@ -149,6 +149,19 @@ int b200seg_set_error_record(unsigned int* host_mapped);
  * MN-major UMMA operand.  `partials` (fprop): float[rows][2][Cout] per-CTA sum / sum of squares
  * of the bf16-rounded output, rows = b200conv_fprop_stat_rows(...). */
 int b200conv_supported(int cin, int cout);
+/* The kernel variant and tiling a conv call of a given shape takes (host-only: no launch, no GPU needed).
+ * op: 0 fprop, 1 dgrad, 2 wgrad, 3 transposed-conv forward, 4 transposed-conv dgrad.
+ * kernel: 0 tap GEMM on square pixel boxes, 1 tap GEMM on halo strips (whole 128-pixel row segments);
+ *         for op 2: 2 split-K wgrad, 3 128-column strip wgrad, 4 row-pair wgrad (other fields unused). */
+typedef struct B200ConvPlan {
+  int kernel, block_k, block_n, n_tiles, ocb;
+  int rows_per_unit;      /* output rows per work unit: 1, 2 (streamed weights) or 4 (vertical taps merged along N) */
+  int weights_resident;   /* the CTA's slice of the filter bank stays in shared memory for its whole life */
+  int private_epilogue;   /* per-warp epilogue pipelines (no CTA-wide barrier per tile) */
+  int staging_bufs, strip_slots, stages, grid, cluster, m_tiles;
+  long long smem_bytes;
+} B200ConvPlan;
+int b200conv_plan(int op, int N, int H, int W, int Cin, int Cout, B200ConvPlan* out);
 int b200conv_fprop_stat_rows(int N, int H, int W, int Cin, int Cout);
 int b200conv_fprop(const void* x, long long ld_x, const void* w, const float* bias, void* y,
                    long long ld_y, int N, int H, int W, int Cin, int Cout, float* partials,
