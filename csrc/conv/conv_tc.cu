@@ -1286,6 +1286,21 @@ static int run_tap_gemm(int mode, const void* a, long long ld_a, const void* w, 
         (H % 4 == 0))
       p.block_n = 64;
   }
+  {
+    // Box mode (rows shorter than 128 pixels) with 128- instead of 256-column tiles: twice the N tiles to spread over
+    // the SMs, at the price of N = 128 instructions and reading each pixel tile twice as often.  Measured per layer
+    // (16 x 64 x 64 ... 16 x 16 x 16, 256 - 1024 channels): 25 - 55 % SLOWER wherever 256-column tiles already fill the
+    // machine, faster only for the 16 x 16 bottleneck (32 pixel tiles x 2 N tiles = 64 CTAs -> 128 CTAs: fprop
+    // 0.035 -> 0.028 ms).  So: only when the 256-column tiling leaves more than half of the SMs idle.
+    // B200SEG_BOX_N=128 / 256 forces one of them (A/B runs).
+    static int bn_env = -1;
+    if (bn_env < 0) { const char* e = getenv("B200SEG_BOX_N"); bn_env = (e == nullptr) ? 0 : (e[0] == '1' ? 128 : 256); }
+    const long long items256 = (long long)p.m_tiles * (n_total / 256);
+    const bool few = 2 * items256 <= kNumSMs;
+    if (!strip && (bn_env == 128 || (bn_env == 0 && few)) && (mode == 0 || mode == 1) && p.ocb == 64 && p.block_n == 256 &&
+        n_total % 128 == 0)
+      p.block_n = 128;
+  }
   if (p.block_n % 32 && p.block_n != 16) return (int)cudaErrorInvalidValue;
   p.n_tiles = (n_total + p.block_n - 1) / p.block_n;
   p.groups = p.block_n / p.ocb;

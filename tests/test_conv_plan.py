@@ -44,6 +44,9 @@ def test_headline_layers_take_the_measured_variants():
     assert (p["kernel"], p["block_n"], p["n_tiles"], p["rows_per_unit"]) == ("tap_gemm/strip", 128, 2, 2)
     for hw, c in ((64, 512), (32, 512), (16, 512)):              # rows shorter than 128 pixels: square pixel boxes
         assert _plan("fprop", N, hw, hw, c, c)["kernel"] == "tap_gemm/box"
+    p = _plan("fprop", N, 16, 16, 512, 512)                      # bottleneck: 32 pixel tiles -> 128-column N tiles (128 CTAs, not 64)
+    assert (p["block_n"], p["n_tiles"], p["grid"]) == (128, 4, 128)
+    assert _plan("fprop", N, 32, 32, 512, 512)["block_n"] == 256  # enough tiles: 256-column N tiles stay
     # weight gradient: row pairs where rows are >= 64 px and Cin <= 512, split-K below / beyond
     assert _plan("wgrad", N, 512, 512, 64, 64)["kernel"] == "wgrad/row-pair"
     assert _plan("wgrad", N, 512, 512, 192, 64)["kernel"] == "wgrad/row-pair"
