@@ -56,6 +56,7 @@ class TrainConfig:
     compress_level: int = 1          # mgzip compresslevel (R:51)
     compress_threads: int = 12       # mgzip thread count (R:43)
     compress_block: int = 1_000_000  # mgzip blocksize (R:51)
+    compress_strategy: str = "default"   # deflate matcher: "default" (the reference's) | "rle" (run-length only: faster and smaller on sparse gradients)
     comm: str = "auto"               # auto | native | fused | torch | star
     overlap: bool = True             # native transport: reduce gradient buckets UNDER backward (R:756-763 does it after)
     bucket_mb: float = 8.0           # bucket size of the overlapped exchange (whole U-Net blocks are never split)

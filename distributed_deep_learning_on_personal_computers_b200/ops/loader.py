@@ -38,12 +38,41 @@ def sources() -> list:
     out = []
     for pat in ("*.cpp", "*.cu", "*/*.cpp", "*/*.cu"):
         out += glob.glob(os.path.join(CSRC_DIR, pat))
-    return sorted(s for s in out if not os.path.basename(s).startswith("standalone_"))
+    # csrc/host/ is plain C++ for the host-side library (build_host), not part of the CUDA extension
+    return sorted(s for s in out if not os.path.basename(s).startswith("standalone_")
+                  and os.path.basename(os.path.dirname(s)) != "host")
+
+
+HOST_LIB_PATH = os.path.join(LIB_DIR, "libb200star.so")
+
+
+def build_host(verbose: bool = False) -> Optional[str]:
+    """Compile the host-side transport (``csrc/host/star_native.cpp``: parallel gzip, framed socket I/O, concurrent
+    gather) into ``lib/libb200star.so`` with the system compiler.  Returns the path, or None when it cannot be built
+    (no g++ / zlib headers): ``parallel.star`` then runs its Python implementation of the same protocol."""
+    import subprocess
+    src = os.path.join(CSRC_DIR, "host", "star_native.cpp")
+    os.makedirs(LIB_DIR, exist_ok=True)
+    tmp = HOST_LIB_PATH + ".tmp"
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-shared", "-fPIC", src, "-o", tmp, "-lz", "-lpthread"]
+    try:
+        res = subprocess.run(cmd, capture_output=True, text=True)
+    except OSError as exc:
+        print(f"[b200seg] host library not built: {exc}")
+        return None
+    if res.returncode != 0:
+        print(f"[b200seg] host library not built:\n{res.stderr[-2000:]}")
+        return None
+    if verbose and res.stderr:
+        print(res.stderr)
+    os.replace(tmp, HOST_LIB_PATH)
+    return HOST_LIB_PATH
 
 
 def build(verbose: bool = False) -> str:
     """Compile every CUDA source for sm_100a and link ``lib/libb200seg.so`` (no GPU needed)."""
     global _tried, _lib_loaded
+    build_host(verbose)
     if _lib_loaded is not None:
         # cpp_extension.load() also LOADS what it built, and a second copy of the same TORCH_LIBRARY in one process
         # aborts: with the library already in, compile in a child process and keep running the loaded one.

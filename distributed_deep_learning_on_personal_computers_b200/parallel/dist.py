@@ -108,7 +108,7 @@ def open_star(cfg):
     retries (R:173-206, with the timeouts the reference lacks)."""
     from . import star
     kw = dict(compress=cfg.compress, level=cfg.compress_level, threads=cfg.compress_threads,
-              block=cfg.compress_block)
+              block=cfg.compress_block, strategy=cfg.compress_strategy)
     port = cfg.master_port + 1
     if cfg.rank == 0:
         srv = star.StarServer(cfg.master_addr, port, cfg.world_size - 1, cfg.timeout_s, **kw)

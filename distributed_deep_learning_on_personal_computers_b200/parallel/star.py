@@ -19,10 +19,18 @@ Differences, all deliberate:
 * timeouts, connect retries, and a ``PeerLost`` exception on EOF instead of ``None`` flowing
   into ``len()`` (SURVEY Q14, 5.3);
 * address and port come from the config / environment, never from a table in the source (Q17).
+
+The byte-moving parts -- block-parallel deflate / inflate, frame send / receive, and the root's gather, which
+reads from ALL workers as their bytes arrive instead of draining them one after the other -- are native
+(``csrc/host/star_native.cpp`` -> ``lib/libb200star.so``, plain C over file descriptors, called through ctypes with
+the GIL released).  The Python versions below are the same protocol and remain as the fallback when the library
+is not built (``B200SEG_STAR_NATIVE=0`` forces them); either side of a connection may use either.
 """
 from __future__ import annotations
 
+import ctypes
 import gzip
+import os
 import socket
 import struct
 import time
@@ -42,19 +50,100 @@ class PeerLost(ConnectionError):
     """The other side closed the connection or stopped answering."""
 
 
+# ---- native byte movers (csrc/host/star_native.cpp) ------------------------------------------
+NATIVE_LIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libb200star.so")
+_ERRORS = {-1: "timed out", -2: "peer closed the connection", -3: "socket error", -4: "message exceeds 4 GiB - 1",
+           -5: "corrupt gzip data", -6: "out of memory"}
+
+
+def _load_native():
+    if os.environ.get("B200SEG_STAR_NATIVE", "1") == "0" or not os.path.exists(NATIVE_LIB):
+        return None
+    try:
+        lib = ctypes.CDLL(NATIVE_LIB, use_errno=True)
+        if lib.star_abi_version() != 2:
+            return None
+    except (OSError, AttributeError):
+        return None
+    u8pp, szp = ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)
+    lib.star_free.argtypes, lib.star_free.restype = [ctypes.c_void_p], None
+    lib.star_deflate.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, u8pp, szp]
+    lib.star_inflate.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int, u8pp, szp]
+    lib.star_send_frame.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int]
+    lib.star_recv_frame.argtypes = [ctypes.c_int, u8pp, szp, ctypes.c_int]
+    lib.star_gather_frames.argtypes = [ctypes.POINTER(ctypes.c_int), ctypes.c_int, u8pp, szp, ctypes.c_int]
+    return lib
+
+
+_native = _load_native()
+
+
+def native_enabled() -> bool:
+    return _native is not None
+
+
+def _take(ptr: ctypes.c_void_p, n: int) -> bytes:
+    try:
+        return ctypes.string_at(ptr, n)
+    finally:
+        _native.star_free(ptr)
+
+
+def _timeout_ms(sock: socket.socket) -> int:
+    t = sock.gettimeout()
+    return -1 if t is None else max(int(t * 1000), 1)
+
+
+def _raise(rc: int, what: str):
+    detail = _ERRORS.get(rc, f"error {rc}")
+    if rc == -3:
+        detail += f" ({os.strerror(ctypes.get_errno())})"
+    if rc in (-4,):
+        raise ValueError(f"{what}: {detail}")
+    if rc in (-5, -6):
+        raise zlib.error(f"{what}: {detail}")
+    raise PeerLost(f"{what}: {detail}")
+
+
 # ---- lossless stage (C2) ---------------------------------------------------------------------
-def deflate(data: bytes, level: int = 1, threads: int = 12, block: int = 1_000_000) -> bytes:
-    """Multi-member gzip, one member per ``block`` bytes, compressed in parallel (R:51)."""
-    if len(data) <= block or threads <= 1:
-        return gzip.compress(data, compresslevel=level, mtime=0)
+STRATEGIES = {"default": 0, "rle": 1}
+
+
+def deflate(data: bytes, level: int = 1, threads: int = 12, block: int = 1_000_000, strategy: str = "default") -> bytes:
+    """Multi-member gzip, one member per ``block`` bytes, compressed in parallel (R:51).  ``strategy="rle"`` restricts
+    deflate to run-length matches: any gzip reader still reads it, and a quantized gradient (mostly runs of zeros)
+    comes out smaller and faster than with zlib's default matcher."""
+    if _native is not None:
+        out, n = ctypes.c_void_p(), ctypes.c_size_t()
+        rc = _native.star_deflate(data, len(data), level, STRATEGIES[strategy], threads, block, ctypes.byref(out),
+                                  ctypes.byref(n))
+        if rc != 0:
+            _raise(rc, "deflate")
+        return _take(out, n.value)
+    def one(c: bytes) -> bytes:
+        if strategy == "default":
+            return gzip.compress(c, compresslevel=level, mtime=0)
+        z = zlib.compressobj(level, zlib.DEFLATED, 31, 8, zlib.Z_RLE)
+        return z.compress(c) + z.flush()
+
+    if len(data) <= block:
+        return one(data)
     chunks = [data[i:i + block] for i in range(0, len(data), block)]
+    if threads <= 1:                                  # same members whatever the thread count: the bytes are reproducible
+        return b"".join(one(c) for c in chunks)
     with ThreadPoolExecutor(max_workers=threads) as pool:
-        parts = list(pool.map(lambda c: gzip.compress(c, compresslevel=level, mtime=0), chunks))
+        parts = list(pool.map(one, chunks))
     return b"".join(parts)
 
 
-def inflate(data: bytes) -> bytes:
+def inflate(data: bytes, threads: int = 12) -> bytes:
     """Inverse of ``deflate``; also reads ``mgzip`` output (ordinary multi-member gzip)."""
+    if _native is not None:
+        out, n = ctypes.c_void_p(), ctypes.c_size_t()
+        rc = _native.star_inflate(data, len(data), threads, ctypes.byref(out), ctypes.byref(n))
+        if rc != 0:
+            _raise(rc, "inflate")
+        return _take(out, n.value)
     out = []
     while data:
         d = zlib.decompressobj(wbits=31)
@@ -104,9 +193,9 @@ def _unpack_hook(d):
 
 
 def pack(obj: Any, compress: bool = True, level: int = 1, threads: int = 12,
-         block: int = 1_000_000) -> bytes:
+         block: int = 1_000_000, strategy: str = "default") -> bytes:
     raw = msgpack.packb(obj, default=_pack_default, use_bin_type=True)
-    return deflate(raw, level, threads, block) if compress else raw
+    return deflate(raw, level, threads, block, strategy) if compress else raw
 
 
 def unpack(data: bytes, compressed: bool = True) -> Any:
@@ -118,6 +207,11 @@ def unpack(data: bytes, compressed: bool = True) -> Any:
 def send_frame(sock: socket.socket, payload: bytes) -> None:
     if len(payload) > MAX_MESSAGE:
         raise ValueError("message exceeds the 4 GiB-1 frame limit of the >I length prefix")
+    if _native is not None:
+        rc = _native.star_send_frame(sock.fileno(), payload, len(payload), _timeout_ms(sock))
+        if rc != 0:
+            _raise(rc, "send failed")
+        return
     try:
         sock.sendall(_LEN.pack(len(payload)) + payload)
     except (BrokenPipeError, ConnectionResetError, socket.timeout) as exc:
@@ -142,20 +236,29 @@ def _recv_exact(sock: socket.socket, n: int) -> bytes:
 
 
 def recv_frame(sock: socket.socket) -> bytes:
+    if _native is not None:
+        out, n = ctypes.c_void_p(), ctypes.c_size_t()
+        rc = _native.star_recv_frame(sock.fileno(), ctypes.byref(out), ctypes.byref(n), _timeout_ms(sock))
+        if rc != 0:
+            _raise(rc, "receive failed")
+        return _take(out, n.value)
     (n,) = _LEN.unpack(_recv_exact(sock, _LEN.size))
     return _recv_exact(sock, n)
 
 
 # ---- endpoints (C4-C8) -----------------------------------------------------------------------
 class _Endpoint:
-    def __init__(self, compress=True, level=1, threads=12, block=1_000_000):
+    def __init__(self, compress=True, level=1, threads=12, block=1_000_000, strategy="default"):
         self.compress, self.level, self.threads, self.block = compress, level, threads, block
+        if strategy not in STRATEGIES:
+            raise ValueError(f"compress_strategy must be one of {sorted(STRATEGIES)}")
+        self.strategy = strategy
         self.bytes_sent = 0
         self.bytes_received = 0
         self.last_raw_bytes = 0
 
     def _send(self, sock, obj):
-        payload = pack(obj, self.compress, self.level, self.threads, self.block)
+        payload = pack(obj, self.compress, self.level, self.threads, self.block, self.strategy)
         self.bytes_sent += len(payload)
         send_frame(sock, payload)
         return len(payload)
@@ -201,14 +304,26 @@ class StarServer(_Endpoint):
 
     def broadcast(self, obj: Any) -> int:
         """Pack once, send to every worker (the reference re-packs per worker)."""
-        payload = pack(obj, self.compress, self.level, self.threads, self.block)
+        payload = pack(obj, self.compress, self.level, self.threads, self.block, self.strategy)
         for c in self.conns:
             send_frame(c, payload)
         self.bytes_sent += len(payload) * len(self.conns)
         return len(payload)
 
     def gather(self) -> List[Any]:
-        return [self._recv(c) for c in self.conns]
+        """One message from every worker, in rank order.  Native: the frames are read concurrently, as bytes arrive
+        on any connection (the reference blocks on worker 0, then 1, ..., R:215-220)."""
+        if _native is None or not self.conns:
+            return [self._recv(c) for c in self.conns]
+        k = len(self.conns)
+        fds = (ctypes.c_int * k)(*[c.fileno() for c in self.conns])
+        outs, lens = (ctypes.c_void_p * k)(), (ctypes.c_size_t * k)()
+        rc = _native.star_gather_frames(fds, k, outs, lens, -1 if self.timeout is None else max(int(self.timeout * 1000), 1))
+        if rc != 0:
+            _raise(rc, "gather failed")
+        payloads = [_take(ctypes.c_void_p(outs[i]), lens[i]) for i in range(k)]
+        self.bytes_received += sum(len(b) for b in payloads)
+        return [unpack(b, self.compress) for b in payloads]
 
     def close(self) -> None:
         for c in self.conns:

@@ -11,6 +11,17 @@ import torch
 from distributed_deep_learning_on_personal_computers_b200.parallel import star
 
 
+@pytest.fixture(params=["native", "python"], autouse=True)
+def impl(request, monkeypatch):
+    """Every test runs against the native byte movers (lib/libb200star.so) and against the Python ones."""
+    if request.param == "native":
+        if not star.native_enabled():
+            pytest.skip("lib/libb200star.so is not built")
+    else:
+        monkeypatch.setattr(star, "_native", None)
+    return request.param
+
+
 def test_deflate_is_multimember_gzip_and_roundtrips():
     data = bytes(range(256)) * 20_000
     z = star.deflate(data, level=1, threads=4, block=1_000_000)
@@ -91,3 +102,135 @@ def test_missing_worker_times_out():
     with pytest.raises(star.PeerLost):
         srv.accept_all()
     srv.close()
+
+
+
+# ---- native / Python interoperability and the native-only paths ------------------------------------------------
+def _python_side(fn, *a, **kw):
+    """Run one star function with the Python implementation regardless of the fixture."""
+    saved, star._native = star._native, None
+    try:
+        return fn(*a, **kw)
+    finally:
+        star._native = saved
+
+
+@pytest.mark.parametrize("size,block", [(0, 1024), (1, 1024), (1023, 1024), (1024, 1024), (1025, 1024),
+                                        (3_000_001, 1_000_000), (5_000_000, 65536)])
+def test_deflate_streams_are_interchangeable(size, block):
+    import numpy as np
+    rng = np.random.default_rng(size)
+    half = rng.integers(0, 256, size // 2, dtype=np.uint8).tobytes()          # incompressible half,
+    data = half + bytes(size - len(half))                                     # then zeros (94 % of a real gradient)
+    z = star.deflate(data, level=1, threads=4, block=block)
+    assert gzip.decompress(z) == data
+    assert star.inflate(z, threads=3) == data
+    assert _python_side(star.inflate, z) == data                              # the other implementation reads it
+    assert star.inflate(_python_side(star.deflate, data, 1, 4, block)) == data
+    foreign = b"".join(gzip.compress(data[i:i + 70_000]) for i in range(0, max(size, 1), 70_000))
+    assert star.inflate(foreign) == data                                      # members without the size field (mgzip, gzip)
+
+
+def test_deflate_is_deterministic():
+    data = bytes(range(256)) * 9000
+    assert star.deflate(data, threads=1, block=100_000) == star.deflate(data, threads=8, block=100_000)
+
+
+def test_corrupt_stream_is_rejected():
+    import zlib
+    z = bytearray(star.deflate(b"payload " * 5000, block=8192))
+    z[len(z) // 2] ^= 0x55
+    with pytest.raises((zlib.error, EOFError, OSError)):
+        star.inflate(bytes(z))
+
+
+def test_large_frame_between_the_two_implementations():
+    a, b = _pair()
+    a.settimeout(10)
+    b.settimeout(10)
+    payload = bytes(range(251)) * 40_000                                       # ~10 MB: many partial sends / receives
+    out = {}
+    th = threading.Thread(target=lambda: out.setdefault("got", _python_side(star.recv_frame, b)))
+    th.start()
+    star.send_frame(a, payload)
+    th.join()
+    assert out["got"] == payload
+    th = threading.Thread(target=lambda: _python_side(star.send_frame, a, payload))
+    th.start()
+    assert star.recv_frame(b) == payload
+    th.join()
+    star.send_frame(a, b"")                                                    # empty frame: just the prefix
+    assert star.recv_frame(b) == b""
+
+
+def test_gather_reads_all_workers_concurrently():
+    """Worker 1 sends late and worker 2 sends a large message first: the gather must not stall on worker 1
+    while worker 2's socket buffer is full (the reference drains the workers strictly in turn, R:215-220)."""
+    srv = star.StarServer("127.0.0.1", 0, n_workers=2, timeout=20)
+    big = torch.arange(3_000_000, dtype=torch.float32)
+    sent = {}
+
+    def worker(rank):
+        w = star.StarWorker("127.0.0.1", srv.port, rank, timeout=20, compress=False)
+        if rank == 1:
+            import time
+            time.sleep(0.3)
+            w.send({"rank": 1, "t": torch.ones(3)})
+        else:
+            w.send({"rank": 2, "t": big})
+            sent["big_done_before_small"] = "small" not in sent
+        sent.setdefault("small" if rank == 1 else "big", True)
+        w.close()
+
+    ths = [threading.Thread(target=worker, args=(r,)) for r in (1, 2)]
+    for t in ths:
+        t.start()
+    srv.compress = False
+    srv.accept_all()
+    msgs = srv.gather()
+    for t in ths:
+        t.join()
+    assert [m["rank"] for m in msgs] == [1, 2] and torch.equal(msgs[1]["t"], big)
+    assert srv.bytes_received > 12_000_000
+    srv.close()
+
+
+def test_gather_times_out_when_a_worker_stays_silent():
+    srv = star.StarServer("127.0.0.1", 0, n_workers=2, timeout=5)
+    ws = {}
+
+    def worker(rank):
+        ws[rank] = star.StarWorker("127.0.0.1", srv.port, rank, timeout=5)
+        if rank == 1:
+            ws[rank].send({"rank": 1})
+
+    ths = [threading.Thread(target=worker, args=(r,)) for r in (1, 2)]
+    for t in ths:
+        t.start()
+    srv.accept_all()
+    for t in ths:
+        t.join()
+    srv.timeout = 0.4
+    for c in srv.conns:
+        c.settimeout(0.4)
+    with pytest.raises(star.PeerLost):
+        srv.gather()
+    for w in ws.values():
+        w.close()
+    srv.close()
+
+
+def test_rle_strategy_is_plain_gzip_and_suits_sparse_gradients():
+    import numpy as np
+    rng = np.random.default_rng(1)
+    g = np.zeros(2_000_000, dtype=np.float16)                                  # a quantized gradient: ~94 % zeros
+    idx = rng.choice(g.size, g.size // 16, replace=False)
+    g[idx] = np.round(rng.standard_normal(idx.size) * 10).astype(np.float16)
+    data = g.tobytes()
+    z_rle = star.deflate(data, threads=4, block=500_000, strategy="rle")
+    z_def = star.deflate(data, threads=4, block=500_000)
+    assert gzip.decompress(z_rle) == data and star.inflate(z_rle) == data
+    assert _python_side(star.inflate, z_rle) == data
+    assert len(z_rle) < 1.1 * len(z_def)                                       # no worse than the default matcher here
+    with pytest.raises(ValueError):
+        star.StarServer("127.0.0.1", 0, n_workers=0, strategy="fastest")
