@@ -19,6 +19,7 @@ plain-PyTorch oracle (``ops.reference``) on CPU, so this file is testable agains
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -66,7 +67,6 @@ class NativeEngine:
         # One pass over the last conv's raw output does its BN+ReLU, the head with loss and backward, and the
         # two sums of that BN's backward (csrc/elem/head_tail.cu); the last activation is never materialised.
         if fused_tail is None:
-            import os
             fused_tail = os.environ.get("B200SEG_HEAD_TAIL", "1") != "0"
         self._want_fused_tail = bool(fused_tail)
         self.bilinear = model.up_sample_mode == "bilinear"
@@ -316,7 +316,6 @@ class NativeEngine:
             self._comm_stream = torch.cuda.Stream(self.device)
             self._ov_events = [torch.cuda.Event() for _ in range(len(ov.ovl_buckets) + 1)]
         self._ov_trigger = {b.trigger: b for b in ov.ovl_buckets if b.trigger is not None}
-        import os
         self._ov_armed = (Fn._conv_impl(self.conv_impl) != "cudnn" and
                           os.environ.get("B200SEG_WGRAD", "tcgen05") != "cudnn")
 
