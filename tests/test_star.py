@@ -234,3 +234,31 @@ def test_rle_strategy_is_plain_gzip_and_suits_sparse_gradients():
     assert len(z_rle) < 1.1 * len(z_def)                                       # no worse than the default matcher here
     with pytest.raises(ValueError):
         star.StarServer("127.0.0.1", 0, n_workers=0, strategy="fastest")
+
+
+def test_inflate_survives_garbage():
+    """Bytes from the network are untrusted: flipped bits, truncation, spliced junk and random headers must end in an
+    exception (or a clean result), never in a crash of the native decoder."""
+    import random
+    import zlib
+    rnd = random.Random(7)
+    base = star.deflate(bytes(rnd.getrandbits(8) for _ in range(20000)) + bytes(30000), block=4096, threads=4)
+    for i in range(400):
+        z = bytearray(base)
+        mode = i % 4
+        if mode == 0:
+            for _ in range(rnd.randint(1, 4)):
+                z[rnd.randrange(len(z))] ^= 1 << rnd.randrange(8)
+        elif mode == 1:
+            z = z[:rnd.randrange(len(z))]
+        elif mode == 2:
+            p = rnd.randrange(len(z))
+            z[p:p + rnd.randint(1, 40)] = bytes(rnd.getrandbits(8) for _ in range(rnd.randint(0, 40)))
+        else:
+            z = bytearray(rnd.getrandbits(8) for _ in range(rnd.randint(0, 300)))
+            if i % 8 == 3:
+                z[:4] = b"\x1f\x8b\x08\x04"
+        try:
+            star.inflate(bytes(z), threads=3)
+        except (zlib.error, EOFError, OSError, ValueError):
+            pass
